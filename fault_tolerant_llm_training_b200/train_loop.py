@@ -1,0 +1,172 @@
+"""Training driver — the counterpart of /root/reference/train.py:12-129.
+
+Same shape (setup -> optional resume -> loop -> every interruption routed to
+`handle_exit` -> exit code 0), same log lines.  Differences, each from a numbered
+quirk in SURVEY.md §9:
+
+  * signal handlers are installed before setup and only set a flag; the loop acts
+    on it at the step boundary after all ranks agree, so a checkpoint never holds
+    a half-applied optimizer step (Q2, Q12);
+  * the injected error fires at the top of step `--error-step`, so "saved at step
+    N" means exactly N updates were applied (Q3);
+  * any non-signal exception is error type -1 (Q4);
+  * checkpoints are loaded strictly and saved atomically with the dataset
+    position (Q5, Q11); resume restores the data position in O(1);
+  * a seed makes all ranks (and resumed jobs) initialise identically (Q7).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+
+import torch
+
+from .cli import model_config_from_args
+from .ckpt.layout import load_checkpoint
+from .config import PRECISION_STR_TO_DTYPE
+from .data.datasets import BatchStream, CollatorForCLM, IterableParquetDataset, ParquetDataset
+from .data.synthetic import write_synthetic_parquet
+from .data.tokenizer import load_tokenizer
+from .ft.exit_handler import handle_exit
+from .ft.signals import (STOP_NONE, SignalFlags, TrainingInterrupt, error_type_of,
+                         stop_code_to_error_type)
+from .log import logger
+from .parallel.env import init_dist
+from .trainer import make_trainer
+
+
+def _build_stream(args, tokenizer, env) -> BatchStream:
+    if not os.path.exists(args.dataset) and args.synthetic_docs > 0:
+        if env.is_main:
+            write_synthetic_parquet(args.dataset, num_docs=args.synthetic_docs,
+                                    max_len=max(128, 2 * args.sequence_length),
+                                    vocab_size=tokenizer.vocab_size)
+        env.barrier()
+    if args.dataset_type == "packed":
+        ds = IterableParquetDataset(args.dataset, tokenizer, args.sequence_length,
+                                    bos_token_id=getattr(tokenizer, "bos_token_id", 1) or 1,
+                                    offset=env.rank, stride=env.world_size)
+        return BatchStream(ds, args.batch_size, rank=env.rank, world_size=env.world_size,
+                           pin_memory=env.device.type == "cuda")
+    ds = ParquetDataset(args.dataset, tokenizer, args.sequence_length,
+                        args.batch_size * args.training_steps * env.world_size)
+    collator = CollatorForCLM(args.sequence_length, tokenizer.pad_token_id)
+    return BatchStream(ds, args.batch_size, collator, rank=env.rank, world_size=env.world_size,
+                       pin_memory=env.device.type == "cuda")
+
+
+def train(args) -> None:
+    flags = SignalFlags().install()  # before setup
+    env = init_dist(args.device)
+    logger.info(f"Experiment args: {args}")
+    model_dtype = PRECISION_STR_TO_DTYPE[args.model_dtype]
+
+    checkpoint = None
+    if args.checkpoint_id:
+        logger.info(f"Loading checkpoint from {args.checkpoint_path}")
+        t0 = time.perf_counter()
+        checkpoint = load_checkpoint(args.checkpoint_path, args.checkpoint_id)
+        logger.info(f"Checkpoint read in {time.perf_counter() - t0:.2f} s")
+
+    logger.info("Setting up DataLoaders...")
+    tokenizer = load_tokenizer(args.tokenizer_name_or_path, args.vocab_size, logger)
+    stream = _build_stream(args, tokenizer, env)
+    if checkpoint is not None:
+        states = checkpoint.get("data_state")
+        if states is not None:
+            st = states[env.rank] if isinstance(states, list) else states
+            stream.load_state_dict(st)
+        else:  # file written by the reference: position = training_step batches (train.py:36-39)
+            stream.fast_forward(int(checkpoint["training_step"]))
+
+    logger.info("Setting up Model...")
+    cfg = model_config_from_args(args, tokenizer.vocab_size)
+    trainer = make_trainer(cfg, env, dtype=model_dtype, lr=args.learning_rate,
+                           warmup_steps=args.lr_warmup_steps, grad_max_norm=args.grad_max_norm,
+                           clip_mode=args.clip_mode, seed=args.seed, parallel=args.parallel,
+                           fused_optimizer=args.fused_optimizer, bucket_mb=args.bucket_mb,
+                           cuda_graph=args.cuda_graph)
+    if checkpoint is not None:
+        trainer.load_state(checkpoint)
+        logger.info("Model loaded from checkpoint")
+        logger.info("Optimizer loaded from checkpoint")
+        logger.info("LR Scheduler loaded from checkpoint")
+        training_step = int(checkpoint["training_step"])
+        logger.info(f"Resuming training from training_step {training_step}")
+    else:
+        training_step = 0
+        logger.info("Starting training!")
+    del checkpoint
+    first_step = training_step
+
+    tokens_per_step = args.batch_size * args.sequence_length * env.world_size
+    t_window, window_steps = time.perf_counter(), 0
+    exit_kw = dict(rank=env.rank, world_size=env.world_size, resubmit_cmd=args.resubmit_cmd,
+                   resume_id=args.checkpoint_id, flags=flags)
+    try:
+        while training_step < args.training_steps:
+            # ---- step boundary: the only place an interruption is acted on ----
+            code = env.max_int(flags.poll()) if env.distributed else flags.poll()
+            if code != STOP_NONE:
+                raise TrainingInterrupt(stop_code_to_error_type(code))
+            if args.raise_error and training_step == args.error_step:
+                # fired *before* the step, so the saved state has exactly `error_step` updates;
+                # a job resumed from that very checkpoint does not re-fire on its first step
+                if not (args.checkpoint_id and training_step == first_step):
+                    raise Exception("Simulated exception to test signal handler", -1)
+            if args.checkpoint_every and training_step > first_step and training_step % args.checkpoint_every == 0:
+                from .ckpt.layout import save_checkpoint
+                from .config import job_id
+                (trainer.save_fn() or save_checkpoint)(
+                    args.checkpoint_path, job_id(), trainer.model, trainer.optimizer, trainer.lr_scheduler,
+                    training_step, data_state=_data_state(stream, env), rank=env.rank,
+                    world_size=env.world_size, logger=logger)
+                logger.info(f"Periodic checkpoint saved at step {training_step}")
+
+            input_ids, labels = next(stream)
+            loss = trainer.step(input_ids, labels)
+
+            window_steps += 1
+            if training_step == 1 or training_step % args.logging_frequency == 0:
+                loss_val = trainer.loss_value(loss)  # device -> host sync, as loss.item() in train.py:116
+                now = time.perf_counter()
+                ms = (now - t_window) * 1e3 / max(window_steps, 1)
+                logger.info(f"Training step: {training_step} | Loss: {loss_val:.2f}")
+                logger.info(f"  step {training_step}: loss {loss_val:.6f} | {ms:.1f} ms/step | "
+                            f"{tokens_per_step / max(ms, 1e-9) * 1e3:.0f} tokens/s | "
+                            f"lr {trainer.optimizer.param_groups[0]['lr']:.4e} | "
+                            f"grad_norm {float(trainer.last_grad_norm):.4f}")
+                t_window, window_steps = time.perf_counter(), 0
+            training_step += 1
+        logger.info("Training completed")
+        if args.save_final:
+            from .ckpt.layout import save_checkpoint
+            from .config import job_id
+            (trainer.save_fn() or save_checkpoint)(
+                args.checkpoint_path, job_id(), trainer.model, trainer.optimizer, trainer.lr_scheduler,
+                training_step, data_state=_data_state(stream, env), rank=env.rank,
+                world_size=env.world_size, logger=logger)
+            logger.info(f"Final checkpoint saved at step {training_step}")
+    except Exception as e:  # noqa: BLE001 — every interruption goes through the same handler (train.py:121-129)
+        error_type = error_type_of(e)
+        if error_type == -1 and not (len(e.args) >= 2 and e.args[1] == -1):
+            logger.exception("Exception in the training loop")
+        handle_exit(trainer.model, trainer.optimizer, trainer.lr_scheduler, training_step,
+                    args.checkpoint_path, error_type, logger,
+                    data_state=_data_state(stream, env) if error_type in (-1, 10) else None,
+                    save_fn=trainer.save_fn(),
+                    made_progress=training_step > first_step, **exit_kw)
+    finally:
+        stream.close()
+        trainer.close()
+        flags.uninstall()
+        env.shutdown()
+    sys.exit(0)  # exit code 0 on every path, as the reference (train.py:119, 129)
+
+
+def _data_state(stream: BatchStream, env):
+    st = stream.state_dict()
+    if env.distributed:
+        return env.gather_objects(st)
+    return st
