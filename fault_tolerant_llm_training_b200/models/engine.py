@@ -1,0 +1,448 @@
+"""B200 execution engine: hand-scheduled forward/backward over the sm_100a kernels.
+
+The reference lets autograd drive ~40 library kernels per layer.  Here one training
+step is a fixed launch sequence over preallocated buffers:
+
+  * parameters, gradients and both Adam moments are four flat bf16 buffers (`FlatState`); the
+    `nn.Parameter`s of the model are views into them, so `state_dict()` / checkpoints are unchanged;
+  * wq|wk|wv are adjacent in the flat buffer, so QKV is one [T, d] x [d, 6144] GEMM and its weight
+    gradient is one GEMM written straight into the gradient buffer (no autograd accumulation pass);
+  * RMSNorm+residual, RoPE, SwiGLU, cross-entropy, grad-norm and AdamW are the fused kernels of
+    csrc/ (each replaces 3-10 ATen kernels of the reference);
+  * activations are saved in static per-layer buffers (8.7 GB at seq 2048 — 180 GB of HBM makes
+    recomputation pointless here), which also makes the step CUDA-graph capturable.
+
+Plain GEMMs go through cuBLAS (`torch.mm(out=)`) unless the tcgen05 kernels of csrc/gemm_*.cu are
+enabled for that shape; attention uses the library SDPA until csrc/attn_*.cu covers it.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional
+
+import torch
+import torch.nn.functional as F
+
+from ..config import ModelConfig
+from ..ops import native as N
+from ..optim.lr import build_lr_scheduler
+from ..parallel.env import DistEnv
+from .llama import Transformer, build_model, flat_size, param_layout
+
+
+# --------------------------------------------------------------------------------------------------
+class FlatState:
+    """Flat bf16 buffers for params / grads / exp_avg / exp_avg_sq with the model's tensors as views."""
+
+    def __init__(self, model: Transformer, device: torch.device, allocator=None):
+        self.layout = param_layout(model)
+        self.numel = flat_size(self.layout)
+        alloc = allocator or (lambda n: torch.zeros(n, dtype=torch.bfloat16, device=device))
+        self.p, self.g = alloc(self.numel), alloc(self.numel)
+        self.m, self.v = alloc(self.numel), alloc(self.numel)
+        self.index = {}
+        params = dict(model.named_parameters())
+        with torch.no_grad():
+            for name, shape, off, n in self.layout:
+                prm = params[name]
+                view = self.p[off:off + n].view(shape)
+                view.copy_(prm.data)
+                prm.data = view
+                prm.grad = self.g[off:off + n].view(shape)
+                self.index[name] = (off, n, shape)
+
+    def view(self, buf: torch.Tensor, name: str) -> torch.Tensor:
+        off, n, shape = self.index[name]
+        return buf[off:off + n].view(shape)
+
+    def span(self, buf: torch.Tensor, first: str, last: str, shape) -> torch.Tensor:
+        """One view covering adjacent tensors first..last (e.g. wq|wk|wv as [6144, 4096])."""
+        o0, _, _ = self.index[first]
+        o1, n1, _ = self.index[last]
+        v = buf[o0:o1 + n1]
+        assert v.numel() == math.prod(shape), "tensors are not adjacent without padding"
+        return v.view(shape)
+
+
+class FlatAdamW(torch.optim.Optimizer):
+    """torch.optim.AdamW-compatible front end over the fused flat kernel (csrc/optim.cu).
+
+    `state_dict()` has exactly torch AdamW's layout (per-parameter `step` fp32 0-d CPU tensor, bf16
+    `exp_avg` / `exp_avg_sq`; param_groups with the same keys), so the reference's
+    `optimizer.load_state_dict(checkpoint["optimizer"])` (train.py:70-72) accepts it and vice versa.
+    """
+
+    def __init__(self, model: Transformer, flat: FlatState, lr: float):
+        defaults = dict(lr=lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, amsgrad=False, maximize=False,
+                        foreach=None, capturable=False, differentiable=False, fused=None,
+                        decoupled_weight_decay=True)
+        super().__init__(list(model.parameters()), defaults)
+        self.flat = flat
+        self.steps_done = 0
+        self._names = [n for n, _ in model.named_parameters()]
+        for name, prm in zip(self._names, self.param_groups[0]["params"]):
+            self.state[prm] = {"step": torch.tensor(0.0, dtype=torch.float32),
+                               "exp_avg": flat.view(flat.m, name), "exp_avg_sq": flat.view(flat.v, name)}
+
+    def hyper_values(self, max_norm: float) -> List[float]:
+        """hyper[8] for the step about to be taken (step count t = steps_done + 1)."""
+        g = self.param_groups[0]
+        b1, b2 = g["betas"]
+        t = self.steps_done + 1
+        return [g["lr"], b1, b2, g["eps"], g["weight_decay"], 1.0 - b1 ** t, math.sqrt(1.0 - b2 ** t), max_norm]
+
+    def zero_grad(self, set_to_none: bool = False) -> None:  # grads are overwritten, never accumulated
+        pass
+
+    @torch.no_grad()
+    def step(self, hyper_dev: torch.Tensor = None, stats_dev: torch.Tensor = None, closure=None):
+        f = self.flat
+        N.adamw_step(f.p, f.g, f.m, f.v, hyper_dev, stats_dev)
+        self.steps_done += 1
+
+    def state_dict(self):
+        for st in self.state.values():
+            st["step"].fill_(float(self.steps_done))
+        return super().state_dict()
+
+    @torch.no_grad()
+    def load_state_dict(self, state_dict) -> None:
+        groups = state_dict["param_groups"]
+        assert len(groups) == 1 and len(groups[0]["params"]) == len(self._names), "parameter count mismatch"
+        for k, v in groups[0].items():
+            if k != "params":
+                self.param_groups[0][k] = v
+        steps = 0
+        for idx, name in zip(groups[0]["params"], self._names):
+            st = state_dict["state"].get(idx)
+            if st is None:
+                continue
+            self.flat.view(self.flat.m, name).copy_(st["exp_avg"])
+            self.flat.view(self.flat.v, name).copy_(st["exp_avg_sq"])
+            steps = max(steps, int(float(st["step"])))
+        self.steps_done = steps
+
+
+# --------------------------------------------------------------------------------------------------
+class LossHandle:
+    """Loss of one step: a pinned host slot + the event recorded after its device->host copy."""
+
+    def __init__(self, host: torch.Tensor, event: torch.cuda.Event):
+        self.host, self.event = host, event
+
+    def item(self) -> float:
+        self.event.synchronize()
+        return float(self.host[0])
+
+    def grad_norm(self) -> float:
+        self.event.synchronize()
+        return float(self.host[1])
+
+    def finite(self) -> bool:
+        self.event.synchronize()
+        return bool(self.host[3] != 0.0)
+
+    def __float__(self) -> float:
+        return self.item()
+
+
+class NativeEngine:
+    """Forward + backward of the decoder for a fixed (batch, seq) shape."""
+
+    def __init__(self, model: Transformer, flat: FlatState, cfg: ModelConfig, batch: int, seq: int,
+                 device: torch.device):
+        self.model, self.flat, self.cfg = model, flat, cfg
+        self.B, self.S, self.T = batch, seq, batch * seq
+        self.dev = device
+        c, T = cfg, self.T
+        d, Fh, H, KV, hd, V = c.dim, c.ffn_hidden, c.n_heads, c.n_kv_heads, c.head_dim, c.vocab_size
+        self.qkv_dim = c.qkv_dim
+        bf = lambda *s: torch.empty(*s, dtype=torch.bfloat16, device=device)
+        f32 = lambda *s: torch.empty(*s, dtype=torch.float32, device=device)
+        L = c.n_layers
+        # saved activations, one set per layer
+        self.x = [bf(T, d) for _ in range(L + 1)]       # block inputs; x[L] = final residual stream
+        self.xn = [bf(T, d) for _ in range(L)]
+        self.rstd1 = [f32(T) for _ in range(L)]
+        self.qkv = [bf(T, self.qkv_dim) for _ in range(L)]
+        self.attn = [None] * L                           # attention outputs (graph-holding tensors)
+        self.attn_in = [None] * L
+        self.ao = bf(T, d)                               # wo output (consumed immediately)
+        self.h = [bf(T, d) for _ in range(L)]
+        self.hn = [bf(T, d) for _ in range(L)]
+        self.rstd2 = [f32(T) for _ in range(L)]
+        self.gate = [bf(T, Fh) for _ in range(L)]
+        self.up = [bf(T, Fh) for _ in range(L)]
+        self.act = [bf(T, Fh) for _ in range(L)]
+        self.ff = bf(T, d)
+        self.xf = bf(T, d)                               # final normed stream
+        self.rstd_f = f32(T)
+        self.logits = bf(T, V)
+        self.row_loss = f32(T)
+        self.loss = f32(1)
+        # backward transients
+        self.dx_a, self.dx_b = bf(T, d), bf(T, d)
+        self.dh = bf(T, d)
+        self.dtmp = bf(T, d)
+        self.dact = bf(T, Fh)
+        self.dgate, self.dup = bf(T, Fh), bf(T, Fh)
+        self.dqkv = bf(T, self.qkv_dim)
+        self.dattn = bf(T, H * hd)
+        self.norm_scratch = f32(N.rmsnorm_partials(T) * d)
+        # rope tables (fp32 [seq, hd/2])
+        self.cos = model.rope_cos[:seq].to(device=device, dtype=torch.float32).contiguous()
+        self.sin = model.rope_sin[:seq].to(device=device, dtype=torch.float32).contiguous()
+        # weight views
+        fv, P, G = flat.view, flat.p, flat.g
+        self.w_emb, self.g_emb = fv(P, "tok_embeddings.weight"), fv(G, "tok_embeddings.weight")
+        self.w_out, self.g_out = fv(P, "output.weight"), fv(G, "output.weight")
+        self.w_fn, self.g_fn = fv(P, "norm.weight"), fv(G, "norm.weight")
+        self.lw = []
+        for i in range(L):
+            b = f"layers.{i}."
+            names = dict(q=b + "attention.wq.weight", v=b + "attention.wv.weight", o=b + "attention.wo.weight",
+                         w1=b + "feed_forward.w1.weight", w2=b + "feed_forward.w2.weight",
+                         w3=b + "feed_forward.w3.weight", an=b + "attention_norm.weight", fn=b + "ffn_norm.weight")
+            lw = {}
+            for buf, tag in ((P, "w"), (G, "g")):
+                lw[tag + "qkv"] = flat.span(buf, names["q"], names["v"], (self.qkv_dim, d))
+                for k in ("o", "w1", "w2", "w3", "an", "fn"):
+                    lw[tag + k] = fv(buf, names[k])
+            self.lw.append(lw)
+
+    # ---- GEMM dispatch: C = A @ B^T (nt), A @ B (nn), A^T @ B (tn) -------------------------------
+    @staticmethod
+    def gemm_nt(a, b, out):
+        return torch.mm(a, b.t(), out=out)
+
+    @staticmethod
+    def gemm_nn(a, b, out, accumulate=False):
+        if accumulate:
+            return torch.addmm(out, a, b, out=out)
+        return torch.mm(a, b, out=out)
+
+    @staticmethod
+    def gemm_tn(a, b, out):
+        return torch.mm(a.t(), b, out=out)
+
+    # ---- attention (library SDPA island; replaced by csrc/attn when available) -------------------
+    def _attention_fwd(self, i: int) -> torch.Tensor:
+        c, B, S = self.cfg, self.B, self.S
+        H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        qkv = self.qkv[i]
+        q = qkv[:, :H * hd].view(B, S, H, hd).transpose(1, 2).detach().requires_grad_()
+        k = qkv[:, H * hd:(H + KV) * hd].view(B, S, KV, hd).transpose(1, 2).detach().requires_grad_()
+        v = qkv[:, (H + KV) * hd:].view(B, S, KV, hd).transpose(1, 2).detach().requires_grad_()
+        with torch.enable_grad():
+            o = F.scaled_dot_product_attention(q, k, v, is_causal=True, enable_gqa=(H != KV))
+        self.attn[i], self.attn_in[i] = o, (q, k, v)
+        return o.transpose(1, 2).reshape(self.T, H * hd)
+
+    def _attention_bwd(self, i: int, dout: torch.Tensor) -> None:
+        c, B, S = self.cfg, self.B, self.S
+        H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        o, (q, k, v) = self.attn[i], self.attn_in[i]
+        do = dout.view(B, S, H, hd).transpose(1, 2)
+        dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
+        d = self.dqkv
+        d[:, :H * hd].view(B, S, H, hd).copy_(dq.transpose(1, 2))
+        d[:, H * hd:(H + KV) * hd].view(B, S, KV, hd).copy_(dk.transpose(1, 2))
+        d[:, (H + KV) * hd:].view(B, S, KV, hd).copy_(dv.transpose(1, 2))
+        self.attn[i] = self.attn_in[i] = None
+
+    # ---- forward ---------------------------------------------------------------------------------
+    @torch.no_grad()
+    def forward(self, tokens: torch.Tensor, labels: torch.Tensor, inv_n: torch.Tensor, write_grad: bool = True):
+        c, T = self.cfg, self.T
+        H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        rot = (H + KV) * hd
+        N.embedding_fwd(tokens.view(-1), self.w_emb, self.x[0])
+        for i, lw in enumerate(self.lw):
+            if i == 0:
+                N.rmsnorm_fwd(self.x[0], lw["wan"], c.norm_eps, self.xn[0], self.rstd1[0])
+            self.gemm_nt(self.xn[i], lw["wqkv"], self.qkv[i])
+            N.rope_inplace(self.qkv[i], self.cos, self.sin, self.S, rot, hd)
+            a = self._attention_fwd(i)
+            self.attn_flat = a
+            self.gemm_nt(a, lw["wo"], self.ao)
+            # h = x + attn_out ; hn = norm(h)
+            N.rmsnorm_fwd(self.x[i], lw["wfn"], c.norm_eps, self.hn[i], self.rstd2[i], delta=self.ao, h_out=self.h[i])
+            self.gemm_nt(self.hn[i], lw["ww1"], self.gate[i])
+            self.gemm_nt(self.hn[i], lw["ww3"], self.up[i])
+            N.swiglu_fwd(self.gate[i], self.up[i], self.act[i])
+            self.gemm_nt(self.act[i], lw["ww2"], self.ff)
+            # x_{i+1} = h + ff ; next norm (attention_norm of layer i+1, or the final norm)
+            if i + 1 < c.n_layers:
+                N.rmsnorm_fwd(self.h[i], self.lw[i + 1]["wan"], c.norm_eps, self.xn[i + 1], self.rstd1[i + 1],
+                              delta=self.ff, h_out=self.x[i + 1])
+            else:
+                N.rmsnorm_fwd(self.h[i], self.w_fn, c.norm_eps, self.xf, self.rstd_f, delta=self.ff,
+                              h_out=self.x[i + 1])
+        self.gemm_nt(self.xf, self.w_out, self.logits)
+        N.cross_entropy(self.logits, labels.view(-1), inv_n, self.row_loss, self.loss, write_grad=write_grad)
+        return self.loss
+
+    # ---- backward (logits already hold d loss / d logits) ---------------------------------------------
+    @torch.no_grad()
+    def backward(self, tokens: torch.Tensor):
+        c, T = self.cfg, self.T
+        H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        rot = (H + KV) * hd
+        L = c.n_layers
+        dl = self.logits
+        self.gemm_tn(dl, self.xf, self.g_out)                     # dW_out
+        self.gemm_nn(dl, self.w_out, self.dtmp)                   # d xf
+        dx, spare = self.dx_a, self.dx_b
+        N.rmsnorm_bwd(self.dtmp, self.x[L], self.w_fn, self.rstd_f, dx, self.g_fn, self.norm_scratch)
+        for i in range(L - 1, -1, -1):
+            lw = self.lw[i]
+            # x_{i+1} = h + w2(act)
+            self.gemm_tn(dx, self.act[i], lw["gw2"])
+            self.gemm_nn(dx, lw["ww2"], self.dact)
+            N.swiglu_bwd(self.dact, self.gate[i], self.up[i], self.dgate, self.dup)
+            self.gemm_tn(self.dgate, self.hn[i], lw["gw1"])
+            self.gemm_tn(self.dup, self.hn[i], lw["gw3"])
+            self.gemm_nn(self.dgate, lw["ww1"], self.dtmp)
+            self.gemm_nn(self.dup, lw["ww3"], self.dtmp, accumulate=True)
+            # dh = dx + d ffn_norm
+            N.rmsnorm_bwd(self.dtmp, self.h[i], lw["wfn"], self.rstd2[i], self.dh, lw["gfn"], self.norm_scratch,
+                          dres=dx)
+            # h = x + wo(attn)
+            a = self.attn[i].transpose(1, 2).reshape(T, H * hd)
+            self.gemm_tn(self.dh, a, lw["go"])
+            self.gemm_nn(self.dh, lw["wo"], self.dattn)
+            self._attention_bwd(i, self.dattn)
+            N.rope_inplace(self.dqkv, self.cos, self.sin, self.S, rot, hd, inverse=True)
+            self.gemm_tn(self.dqkv, self.xn[i], lw["gqkv"])
+            self.gemm_nn(self.dqkv, lw["wqkv"], self.dtmp)
+            N.rmsnorm_bwd(self.dtmp, self.x[i], lw["wan"], self.rstd1[i], spare, lw["gan"], self.norm_scratch,
+                          dres=self.dh)
+            dx, spare = spare, dx
+        # embedding: deterministic scatter-add
+        self.g_emb.zero_()
+        sorted_tok, perm = torch.sort(tokens.view(-1), stable=True)
+        N.embedding_bwd(sorted_tok, perm, dx, self.g_emb)
+
+
+# --------------------------------------------------------------------------------------------------
+class NativeTrainer:
+    """`.step(inputs, labels)` on a B200: staged H2D, fwd, bwd, grad norm (+clip), fused AdamW, LR step."""
+
+    RING = 4
+
+    def __init__(self, cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
+                 grad_max_norm: float, clip_mode: str = "clip", seed: int = 0, parallel: str = "none",
+                 bucket_mb: int = 512, cuda_graph: bool = False):
+        if dtype != torch.bfloat16:
+            raise ValueError("the B200 engine is bf16-only (use --device cpu for other dtypes)")
+        N.lib()  # fail loudly if the sm_100a library is missing
+        self.cfg, self.env, self.device = cfg, env, env.device
+        self.parallel = parallel
+        self.grad_max_norm, self.clip_mode = float(grad_max_norm), clip_mode
+        self.model = build_model(cfg, dtype, self.device, seed=seed)
+        self.model.train()
+        self.flat = self._make_flat_state()
+        self.optimizer = FlatAdamW(self.model, self.flat, lr)
+        self.lr_scheduler = build_lr_scheduler(self.optimizer, warmup_steps)
+        self.engine: Optional[NativeEngine] = None
+        self.hyper = torch.zeros(8, dtype=torch.float32, device=self.device)
+        self.stats = torch.zeros(4, dtype=torch.float32, device=self.device)
+        self.gn_scratch = torch.zeros(N.grad_norm_partials(), dtype=torch.float32, device=self.device)
+        self.result_dev = torch.zeros(4, dtype=torch.float32, device=self.device)
+        self.result_host = [torch.zeros(4, dtype=torch.float32).pin_memory() for _ in range(self.RING)]
+        self.events = [torch.cuda.Event() for _ in range(self.RING)]
+        self._slot = 0
+        self._stage = None
+        self._pending: List[LossHandle] = []   # results not yet inspected by the host (at most 2)
+        self.last_grad_norm = 0.0
+        self.h2d_bytes_per_step = 0
+        self.d2h_bytes_per_step = 16
+        self.kernel_launches_per_step = 0
+
+    def _make_flat_state(self) -> FlatState:
+        return FlatState(self.model, self.device)
+
+    # -- per-shape setup --------------------------------------------------------------------------
+    def _ensure_engine(self, B: int, S: int) -> None:
+        if self.engine is not None and (self.engine.B, self.engine.S) == (B, S):
+            return
+        self.engine = NativeEngine(self.model, self.flat, self.cfg, B, S, self.device)
+        T = B * S
+        nbytes = 2 * T * 8 + 64
+        # staging ring: [tokens | labels | inv_n, hyper[8]] packed so that a step needs ONE H2D copy.  The host
+        # runs at most two steps ahead of the GPU (see step()), so a ring of RING slots is never overwritten
+        # while its copy is in flight.
+        self._stage = []
+        for _ in range(self.RING):
+            host = torch.zeros(nbytes, dtype=torch.uint8).pin_memory()
+            dev = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
+            self._stage.append(dict(
+                host=host, dev=dev,
+                tok_h=host[:T * 8].view(torch.int64).view(B, S), lab_h=host[T * 8:2 * T * 8].view(torch.int64).view(B, S),
+                flt_h=host[2 * T * 8:].view(torch.float32),
+                tok_d=dev[:T * 8].view(torch.int64).view(B, S), lab_d=dev[T * 8:2 * T * 8].view(torch.int64).view(B, S),
+                flt_d=dev[2 * T * 8:].view(torch.float32)))
+        self.h2d_bytes_per_step = nbytes
+
+    def _global_token_count(self, n_local: int) -> int:
+        return self.env.sum_int(n_local)
+
+    # -- one step (reference: train.py:93-110) ----------------------------------------------------
+    def step(self, inputs: torch.Tensor, labels: torch.Tensor) -> LossHandle:
+        B, S = inputs.shape
+        self._ensure_engine(B, S)
+        launches0 = N.LAUNCHES
+        # results are inspected two steps late, so the host never drains the GPU queue; a non-finite
+        # gradient norm made that step's update a no-op on the device (csrc/optim.cu), so raising late
+        # still checkpoints clean state (reference: get_total_norm(error_if_nonfinite=True), utils.py:61)
+        while len(self._pending) >= 2:
+            old = self._pending.pop(0)
+            if not old.finite():
+                raise FloatingPointError("The total norm of gradients is non-finite, so it cannot be clipped.")
+            self.last_grad_norm = old.grad_norm()
+        n_items = self._global_token_count(int(labels.ne(-100).sum()))
+        slot = self._slot
+        self._slot = (slot + 1) % self.RING
+        st = self._stage[slot]
+        st["tok_h"].copy_(inputs)
+        st["lab_h"].copy_(labels)
+        flt = [1.0 / max(n_items, 1)] + self.optimizer.hyper_values(self.grad_max_norm)
+        st["flt_h"][:len(flt)] = torch.tensor(flt, dtype=torch.float32)
+        st["dev"].copy_(st["host"], non_blocking=True)                  # the one H2D copy of the step
+        inv_n, hyper = st["flt_d"][0:1], st["flt_d"][1:9]
+        loss = self.engine.forward(st["tok_d"], st["lab_d"], inv_n)
+        self.engine.backward(st["tok_d"])
+        self._reduce_and_update(hyper, loss)
+        self.lr_scheduler.step()
+        # result: loss, grad norm, clip coef, finite
+        self.result_dev[0:1].copy_(loss)
+        self.result_dev[1:4].copy_(self.stats[0:3])
+        self.result_host[slot].copy_(self.result_dev, non_blocking=True)  # the one D2H copy of the step
+        self.events[slot].record()
+        handle = LossHandle(self.result_host[slot], self.events[slot])
+        self._pending.append(handle)
+        self.kernel_launches_per_step = N.LAUNCHES - launches0
+        return handle
+
+    def _reduce_and_update(self, hyper: torch.Tensor, loss: torch.Tensor) -> None:
+        """Single-GPU: grad norm over the flat gradient, then the fused AdamW pass."""
+        f = self.flat
+        N.grad_norm(f.g, hyper, self.gn_scratch, self.stats, clip=(self.clip_mode == "clip"))
+        self.optimizer.step(hyper, self.stats)
+
+    # -- checkpoint plumbing ----------------------------------------------------------------------
+    def load_state(self, ckpt: dict) -> None:
+        self.model.load_state_dict(ckpt["model"], strict=True)  # copies into the flat views
+        self.optimizer.load_state_dict(ckpt["optimizer"])
+        self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
+
+    def save_fn(self):
+        return None
+
+    def loss_value(self, loss: LossHandle) -> float:
+        v = loss.item()
+        self.last_grad_norm = loss.grad_norm()
+        return v
+
+    def close(self) -> None:
+        pass

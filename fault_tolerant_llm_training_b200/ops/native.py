@@ -1,0 +1,176 @@
+"""ctypes binding of libftl_b200.so (C ABI in include/ftl_b200.h).
+
+The library has no dependency on libtorch: tensors cross the boundary as raw device pointers plus the
+current CUDA stream handle, so every launch lands on the stream PyTorch is using (and is captured by
+CUDA graphs like any other launch).  Loading fails loudly: on a GPU box a missing or stale library
+is an error, never a silent fallback to PyTorch ops.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_float, c_int, c_int64, c_void_p
+from typing import Optional
+
+import torch
+
+_LIB: Optional[ctypes.CDLL] = None
+LAUNCHES = 0  # native calls made through this module
+KERNELS = 0   # kernels of libftl_b200.so launched through this module (bench.py reports the delta)
+
+PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(PKG_DIR, "_native", "libftl_b200.so")
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _sig(lib, name, argtypes, restype=c_int):
+    fn = getattr(lib, name)
+    fn.argtypes, fn.restype = argtypes, restype
+    return fn
+
+
+def lib() -> ctypes.CDLL:
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        if os.environ.get("FTL_NO_AUTOBUILD"):
+            raise NativeError(f"{LIB_PATH} is missing; run `python -m fault_tolerant_llm_training_b200.build`")
+        from ..build import build
+
+        build()
+    L = ctypes.CDLL(LIB_PATH)
+    P, I, I64, F = c_void_p, c_int, c_int64, c_float
+    _sig(L, "ftl_rmsnorm_fwd", [P, P, P, P, P, P, I, I, F, P])
+    _sig(L, "ftl_rmsnorm_partials", [I])
+    _sig(L, "ftl_rmsnorm_bwd", [P, P, P, P, P, P, P, P, I, I, P])
+    _sig(L, "ftl_rope_inplace", [P, P, P, I64, I, I, I, I, I, P])
+    _sig(L, "ftl_swiglu_fwd", [P, P, P, I64, P])
+    _sig(L, "ftl_swiglu_bwd", [P, P, P, P, P, I64, P])
+    _sig(L, "ftl_embedding_fwd", [P, P, P, I64, I, I, P])
+    _sig(L, "ftl_embedding_bwd", [P, P, P, P, I64, I, I, P])
+    _sig(L, "ftl_cross_entropy", [P, P, P, P, P, P, I64, I, I64, I, P])
+    _sig(L, "ftl_grad_norm_partials", [])
+    _sig(L, "ftl_grad_norm", [P, I64, P, P, P, I, P])
+    _sig(L, "ftl_adamw_step", [P, P, P, P, I64, P, P, P])
+    for name, sig in _OPTIONAL.items():
+        if hasattr(L, name):
+            _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
+    _LIB = L
+    return L
+
+
+# entry points added by later build stages register here: name -> (argtypes[, restype])
+_OPTIONAL: dict = {}
+
+
+def has(name: str) -> bool:
+    return hasattr(lib(), name)
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else c_void_p(t.data_ptr())
+
+
+def _stream():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _check(code: int, what: str, kernels: int = 1) -> None:
+    global LAUNCHES, KERNELS
+    LAUNCHES += 1
+    KERNELS += kernels
+    if code != 0:
+        raise NativeError(f"{what} failed with CUDA error {code}")
+
+
+def _bf16(*ts):
+    for t in ts:
+        if t is not None:
+            assert t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous(), (t.dtype, t.shape, t.stride())
+
+
+# ------------------------------------------------------------------------------------------------
+def rmsnorm_fwd(x, w, eps, y, rstd=None, delta=None, h_out=None):
+    """y = rmsnorm(x [+ delta]); when delta is given, h_out receives x + delta."""
+    _bf16(x, w, y, delta, h_out)
+    rows, dim = x.shape
+    _check(lib().ftl_rmsnorm_fwd(_ptr(x), _ptr(delta), _ptr(h_out), _ptr(w), _ptr(y), _ptr(rstd), rows, dim,
+                                 float(eps), _stream()), "ftl_rmsnorm_fwd")
+    return y
+
+
+def rmsnorm_partials(rows: int) -> int:
+    return lib().ftl_rmsnorm_partials(rows)
+
+
+def rmsnorm_bwd(dy, x, w, rstd, dx, dw, scratch, dres=None):
+    _bf16(dy, x, w, dx, dw, dres)
+    rows, dim = x.shape
+    assert scratch.dtype == torch.float32 and scratch.numel() >= rmsnorm_partials(rows) * dim
+    _check(lib().ftl_rmsnorm_bwd(_ptr(dy), _ptr(x), _ptr(w), _ptr(rstd), _ptr(dres), _ptr(dx), _ptr(dw),
+                                 _ptr(scratch), rows, dim, _stream()), "ftl_rmsnorm_bwd", 2)
+    return dx
+
+
+def rope_inplace(qkv, cos, sin, seq_len, rot_cols, head_dim, inverse=False):
+    """qkv: [tokens, row] bf16; rotates columns [0, rot_cols) (the q heads then the k heads)."""
+    assert qkv.dtype == torch.bfloat16 and qkv.stride(1) == 1 and cos.dtype == torch.float32
+    tokens, _ = qkv.shape
+    _check(lib().ftl_rope_inplace(_ptr(qkv), _ptr(cos), _ptr(sin), tokens, seq_len, qkv.stride(0), rot_cols,
+                                  head_dim, int(inverse), _stream()), "ftl_rope_inplace")
+    return qkv
+
+
+def swiglu_fwd(gate, up, act):
+    _bf16(gate, up, act)
+    _check(lib().ftl_swiglu_fwd(_ptr(gate), _ptr(up), _ptr(act), gate.numel(), _stream()), "ftl_swiglu_fwd")
+    return act
+
+
+def swiglu_bwd(dact, gate, up, dgate, dup):
+    _bf16(dact, gate, up, dgate, dup)
+    _check(lib().ftl_swiglu_bwd(_ptr(dact), _ptr(gate), _ptr(up), _ptr(dgate), _ptr(dup), gate.numel(), _stream()),
+           "ftl_swiglu_bwd")
+
+
+def embedding_fwd(tokens, table, out):
+    _bf16(table, out)
+    assert tokens.dtype == torch.int64 and tokens.is_contiguous()
+    _check(lib().ftl_embedding_fwd(_ptr(tokens), _ptr(table), _ptr(out), tokens.numel(), table.shape[1],
+                                   table.shape[0], _stream()), "ftl_embedding_fwd")
+    return out
+
+
+def embedding_bwd(sorted_tokens, perm, dout, dtable):
+    _bf16(dout, dtable)
+    _check(lib().ftl_embedding_bwd(_ptr(sorted_tokens), _ptr(perm), _ptr(dout), _ptr(dtable), sorted_tokens.numel(),
+                                   dtable.shape[1], dtable.shape[0], _stream()), "ftl_embedding_bwd")
+
+
+def cross_entropy(logits, labels, inv_n, row_loss, loss_out, row_lse=None, write_grad=True):
+    """In place: logits [rows, V] bf16 become d(loss)/d(logits).  loss_out[0] = sum(CE) * inv_n."""
+    assert logits.dtype == torch.bfloat16 and logits.stride(1) == 1 and labels.dtype == torch.int64
+    rows, vocab = logits.shape
+    _check(lib().ftl_cross_entropy(_ptr(logits), _ptr(labels), _ptr(inv_n), _ptr(row_loss), _ptr(row_lse),
+                                   _ptr(loss_out), rows, vocab, logits.stride(0), int(write_grad), _stream()),
+           "ftl_cross_entropy", 2 if loss_out is not None else 1)
+
+
+def grad_norm_partials() -> int:
+    return lib().ftl_grad_norm_partials()
+
+
+def grad_norm(g_flat, hyper, scratch, stats, clip=True):
+    _bf16(g_flat)
+    _check(lib().ftl_grad_norm(_ptr(g_flat), g_flat.numel(), _ptr(hyper), _ptr(scratch), _ptr(stats), int(clip),
+                               _stream()), "ftl_grad_norm", 2)
+
+
+def adamw_step(p, g, m, v, hyper, stats=None):
+    _bf16(p, g, m, v)
+    _check(lib().ftl_adamw_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), _ptr(hyper), _ptr(stats), _stream()),
+           "ftl_adamw_step")

@@ -1,0 +1,71 @@
+"""The hand-scheduled B200 engine against autograd on the portable model (same weights, same batch)."""
+import pytest
+import torch
+
+from fault_tolerant_llm_training_b200.config import ModelConfig
+from fault_tolerant_llm_training_b200.models.llama import build_model
+from fault_tolerant_llm_training_b200.ops import torch_ops as T
+from fault_tolerant_llm_training_b200.parallel.env import DistEnv
+
+pytestmark = pytest.mark.gpu
+
+CFG = ModelConfig(dim=256, n_layers=2, n_heads=4, n_kv_heads=2, multiple_of=64, ffn_dim_multiplier=1.3,
+                  seq_len=64, vocab_size=1024)
+
+
+def _trainer(**kw):
+    from fault_tolerant_llm_training_b200.models.engine import NativeTrainer
+    env = DistEnv(device=torch.device("cuda:0"))
+    args = dict(dtype=torch.bfloat16, lr=1e-3, warmup_steps=2, grad_max_norm=1.0, seed=11)
+    args.update(kw)
+    return NativeTrainer(CFG, env, **args)
+
+
+def _batch(seed=0, B=2):
+    g = torch.Generator().manual_seed(seed)
+    tok = torch.randint(0, CFG.vocab_size, (B, CFG.seq_len + 1), generator=g)
+    inputs, labels = tok[:, :-1].contiguous(), tok[:, 1:].clone()
+    labels[:, :5] = -100
+    return inputs, labels
+
+
+def test_engine_loss_and_grads_match_autograd():
+    tr = _trainer()
+    ref = build_model(CFG, torch.float32, "cuda", seed=0)
+    ref.load_state_dict({k: v.float() for k, v in tr.model.state_dict().items()})
+    inputs, labels = _batch()
+    tr._ensure_engine(*inputs.shape)
+    n = int(labels.ne(-100).sum())
+    inv_n = torch.tensor([1.0 / n], device="cuda")
+    loss = tr.engine.forward(inputs.cuda(), labels.cuda(), inv_n)
+    tr.engine.backward(inputs.cuda())
+    ref_loss = T.cross_entropy_sum(ref(inputs.cuda()), labels.cuda()) / n
+    ref_loss.backward()
+    assert abs(float(loss) - float(ref_loss)) < 3e-2 * max(1.0, abs(float(ref_loss)))
+    for (name, p), (_, q) in zip(tr.model.named_parameters(), ref.named_parameters()):
+        g, r = p.grad.float(), q.grad
+        err = (g - r).norm() / (r.norm() + 1e-12)
+        assert err < 5e-2, (name, float(err))
+
+
+def test_trainer_steps_reduce_loss_and_checkpoint_roundtrip(tmp_path):
+    from fault_tolerant_llm_training_b200.ckpt.layout import load_checkpoint, save_checkpoint
+    tr = _trainer()
+    inputs, labels = _batch(1)
+    losses = [tr.step(inputs, labels).item() for _ in range(8)]
+    assert losses[-1] < losses[0]
+    assert tr.kernel_launches_per_step > 0
+    save_checkpoint(str(tmp_path), "7", tr.model, tr.optimizer, tr.lr_scheduler, 8)
+    ck = load_checkpoint(str(tmp_path), "7")
+    assert len(ck["model"]) == 3 + 9 * CFG.n_layers
+    assert all(int(s["step"]) == 8 for s in ck["optimizer"]["state"].values())
+    tr2 = _trainer(seed=99)
+    tr2.load_state(ck)
+    a = tr.step(inputs, labels).item()
+    b = tr2.step(inputs, labels).item()
+    assert a == b  # bitwise-identical continuation after a save/load round trip
+    for p, q in zip(tr.model.parameters(), tr2.model.parameters()):
+        assert torch.equal(p, q)
+    # the torch-AdamW layout loads into a stock torch optimizer too (what the reference does on resume)
+    opt = torch.optim.AdamW(build_model(CFG, torch.bfloat16, "cpu").parameters(), lr=1e-3)
+    opt.load_state_dict(ck["optimizer"])

@@ -1,0 +1,154 @@
+"""T1: each sm_100a kernel against a plain fp32 PyTorch statement of the same op."""
+import math
+
+import pytest
+import torch
+
+from fault_tolerant_llm_training_b200.ops import torch_ops as T
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def N():
+    from fault_tolerant_llm_training_b200.ops import native
+    native.lib()
+    return native
+
+
+def bf(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    return (torch.randn(*shape, device=DEV, generator=g) * scale).to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("rows,dim", [(64, 256), (300, 4096), (17, 1024), (5, 8192)])
+def test_rmsnorm_fwd_matches_reference_rounding(N, rows, dim):
+    x, w = bf(rows, dim, seed=1), bf(dim, seed=2) * 0.1 + 1
+    y, rstd = torch.empty_like(x), torch.empty(rows, device=DEV)
+    N.rmsnorm_fwd(x, w, 1e-5, y, rstd)
+    ref = T.rmsnorm(x, w, 1e-5)
+    torch.testing.assert_close(y.float(), ref.float(), rtol=1.6e-2, atol=1e-2)
+    assert (y != ref).float().mean() < 0.02  # same rounding points: almost always bit-equal
+    torch.testing.assert_close(rstd, torch.rsqrt(x.float().pow(2).mean(-1) + 1e-5), rtol=1e-5, atol=1e-6)
+    # fused residual add
+    d = bf(rows, dim, seed=3)
+    h, y2 = torch.empty_like(x), torch.empty_like(x)
+    N.rmsnorm_fwd(x, w, 1e-5, y2, rstd, delta=d, h_out=h)
+    assert torch.equal(h, x + d)
+    torch.testing.assert_close(y2.float(), T.rmsnorm(x + d, w, 1e-5).float(), rtol=1.6e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize("rows,dim", [(64, 256), (2048, 4096), (301, 1024)])
+def test_rmsnorm_bwd(N, rows, dim):
+    x, w, dy, dres = bf(rows, dim, seed=1), bf(dim, seed=2) * 0.1 + 1, bf(rows, dim, seed=3), bf(rows, dim, seed=4)
+    xf = x.float().requires_grad_()
+    wf = w.float().requires_grad_()
+    inv = torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5)
+    (xf * inv * wf).backward(dy.float())
+    rstd = inv.detach().squeeze(-1).contiguous()
+    dx, dw = torch.empty_like(x), torch.empty_like(w)
+    scratch = torch.empty(N.rmsnorm_partials(rows) * dim, device=DEV)
+    N.rmsnorm_bwd(dy, x, w, rstd, dx, dw, scratch)
+    torch.testing.assert_close(dx.float(), xf.grad, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(dw.float(), wf.grad, rtol=2e-2, atol=2e-2 * math.sqrt(rows))
+    N.rmsnorm_bwd(dy, x, w, rstd, dx, dw, scratch, dres=dres)
+    torch.testing.assert_close(dx.float(), xf.grad + dres.float(), rtol=2e-2, atol=3e-2)
+
+
+@pytest.mark.parametrize("B,S,H,KV,hd", [(2, 64, 4, 2, 64), (1, 2048, 32, 8, 128)])
+def test_rope_inplace_and_inverse(N, B, S, H, KV, hd):
+    width = (H + 2 * KV) * hd
+    qkv = bf(B * S, width, seed=5)
+    orig = qkv.clone()
+    cos, sin = T.rope_table(hd, S, 500000.0, device=DEV)
+    N.rope_inplace(qkv, cos, sin, S, (H + KV) * hd, hd)
+    q = orig[:, :H * hd].view(B, S, H, hd)
+    k = orig[:, H * hd:(H + KV) * hd].view(B, S, KV, hd)
+    assert torch.equal(qkv[:, :H * hd].view(B, S, H, hd), T.rope_apply(q, cos, sin))
+    assert torch.equal(qkv[:, H * hd:(H + KV) * hd].view(B, S, KV, hd), T.rope_apply(k, cos, sin))
+    assert torch.equal(qkv[:, (H + KV) * hd:], orig[:, (H + KV) * hd:])  # v untouched
+    N.rope_inplace(qkv, cos, sin, S, (H + KV) * hd, hd, inverse=True)
+    torch.testing.assert_close(qkv.float(), orig.float(), rtol=2e-2, atol=2e-2)
+
+
+def test_swiglu_fwd_bwd(N):
+    g, u, d = bf(512, 1024, seed=1), bf(512, 1024, seed=2), bf(512, 1024, seed=3)
+    act = torch.empty_like(g)
+    N.swiglu_fwd(g, u, act)
+    ref = T.swiglu(g, u)
+    torch.testing.assert_close(act.float(), ref.float(), rtol=1.6e-2, atol=1e-2)
+    gf, uf = g.float().requires_grad_(), u.float().requires_grad_()
+    (torch.nn.functional.silu(gf) * uf).backward(d.float())
+    dg, du = torch.empty_like(g), torch.empty_like(g)
+    N.swiglu_bwd(d, g, u, dg, du)
+    torch.testing.assert_close(dg.float(), gf.grad, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(du.float(), uf.grad, rtol=2e-2, atol=2e-2)
+
+
+def test_embedding_fwd_bwd_deterministic(N):
+    V, D, n = 1000, 256, 4096
+    table = bf(V, D, seed=1)
+    tok = torch.randint(0, V, (n,), device=DEV, generator=torch.Generator(device=DEV).manual_seed(3))
+    out = torch.empty(n, D, device=DEV, dtype=torch.bfloat16)
+    N.embedding_fwd(tok, table, out)
+    assert torch.equal(out, table[tok])
+    dout = bf(n, D, seed=2)
+    ref = torch.zeros(V, D, device=DEV).index_add_(0, tok, dout.float())
+    runs = []
+    for _ in range(2):
+        dt = torch.zeros(V, D, device=DEV, dtype=torch.bfloat16)
+        s, p = torch.sort(tok, stable=True)
+        N.embedding_bwd(s, p, dout, dt)
+        runs.append(dt)
+    torch.testing.assert_close(runs[0].float(), ref, rtol=2e-2, atol=3e-2)
+    assert torch.equal(runs[0], runs[1])
+
+
+@pytest.mark.parametrize("rows,V", [(64, 1024), (256, 131072)])
+def test_cross_entropy_fwd_bwd(N, rows, V):
+    logits = bf(rows, V, scale=2.0, seed=7)
+    labels = torch.randint(0, V, (rows,), device=DEV)
+    labels[::5] = -100
+    n = int((labels != -100).sum())
+    lf = logits.float().requires_grad_()
+    ref_loss = torch.nn.functional.cross_entropy(lf, labels, reduction="sum") / n
+    ref_loss.backward()
+    inv_n = torch.tensor([1.0 / n], device=DEV)
+    row_loss, loss = torch.empty(rows, device=DEV), torch.empty(1, device=DEV)
+    work = logits.clone()
+    N.cross_entropy(work, labels, inv_n, row_loss, loss)
+    torch.testing.assert_close(loss[0], ref_loss.detach(), rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(work.float(), lf.grad, rtol=2e-2, atol=1e-6)
+    assert (work[labels == -100] == 0).all()
+
+
+def test_grad_norm_and_adamw_match_torch(N):
+    n = 1 << 20
+    p, g = bf(n, seed=1), bf(n, scale=0.01, seed=2)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    ref_p = torch.nn.Parameter(p.float().clone())
+    opt = torch.optim.AdamW([ref_p], lr=1e-2)
+    scratch, stats = torch.empty(N.grad_norm_partials(), device=DEV), torch.zeros(4, device=DEV)
+    for t in range(1, 4):
+        hyper = torch.tensor([1e-2, 0.9, 0.999, 1e-8, 1e-2, 1 - 0.9 ** t, math.sqrt(1 - 0.999 ** t), 1.0], device=DEV)
+        N.grad_norm(g, hyper, scratch, stats, clip=True)
+        norm = g.float().norm()
+        torch.testing.assert_close(stats[0], norm, rtol=1e-4, atol=1e-5)
+        coef = min(1.0, 1.0 / (float(norm) + 1e-6))
+        assert abs(float(stats[1]) - coef) < 1e-4 and float(stats[2]) == 1.0
+        N.adamw_step(p, g, m, v, hyper, stats)
+        ref_p.grad = g.float() * coef
+        opt.step()
+    # bf16 state vs fp32 reference: a few ulps of bf16
+    torch.testing.assert_close(p.float(), ref_p.detach(), rtol=2e-2, atol=2e-2)
+    st = opt.state[ref_p]
+    torch.testing.assert_close(m.float(), st["exp_avg"], rtol=3e-2, atol=1e-4)
+    torch.testing.assert_close(v.float(), st["exp_avg_sq"], rtol=3e-2, atol=1e-7)
+    # a non-finite gradient makes the update a no-op
+    g2 = g.clone(); g2[5] = float("inf")
+    before = p.clone()
+    N.grad_norm(g2, hyper, scratch, stats, clip=True)
+    N.adamw_step(p, g2, m, v, hyper, stats)
+    assert float(stats[2]) == 0.0 and torch.equal(p, before)
