@@ -66,8 +66,11 @@ def test_rope_inplace_and_inverse(N, B, S, H, KV, hd):
     N.rope_inplace(qkv, cos, sin, S, (H + KV) * hd, hd)
     q = orig[:, :H * hd].view(B, S, H, hd)
     k = orig[:, H * hd:(H + KV) * hd].view(B, S, KV, hd)
-    assert torch.equal(qkv[:, :H * hd].view(B, S, H, hd), T.rope_apply(q, cos, sin))
-    assert torch.equal(qkv[:, H * hd:(H + KV) * hd].view(B, S, KV, hd), T.rope_apply(k, cos, sin))
+    # fp32 math rounded once to bf16 on both sides; nvcc contracts a*c - b*s into an FMA, so allow one bf16 ulp
+    for got, want in ((qkv[:, :H * hd].view(B, S, H, hd), T.rope_apply(q, cos, sin)),
+                      (qkv[:, H * hd:(H + KV) * hd].view(B, S, KV, hd), T.rope_apply(k, cos, sin))):
+        torch.testing.assert_close(got.float(), want.float(), rtol=8e-3, atol=1e-3)
+        assert (got != want).float().mean() < 0.01
     assert torch.equal(qkv[:, (H + KV) * hd:], orig[:, (H + KV) * hd:])  # v untouched
     N.rope_inplace(qkv, cos, sin, S, (H + KV) * hd, hd, inverse=True)
     torch.testing.assert_close(qkv.float(), orig.float(), rtol=2e-2, atol=2e-2)
