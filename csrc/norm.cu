@@ -9,6 +9,7 @@
 // grid stride and keeps its slice of d(weight) in registers, then writes one fp32 partial row into
 // scratch; a second kernel folds the partials in fixed order (deterministic, no atomics).
 #include "common/util.cuh"
+#include <cstdio>
 
 namespace ftl {
 
@@ -178,4 +179,96 @@ FTL_API int ftl_rmsnorm_bwd(const void* dy, const void* x, const void* w, const 
     rmsnorm_dw_finalize_kernel<<<(dim + 255) / 256, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw);
     FTL_LAUNCH_CHECK();
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// RMSNorm backward for callers that have no device memory to hand in as scratch.
+//
+// ftl_rmsnorm_bwd() needs an fp32 work area of ftl_rmsnorm_partials(rows) x dim floats from its caller.
+// Some callers cannot produce one.  The case this library cares about is the recovery path of a training
+// job: after a CUDA out-of-memory error the handler still has to run a backward fragment or a
+// finiteness check before it snapshots state, and at that moment every further cudaMalloc fails — the
+// framework's own caching allocator already owns what is left of the device.  The same holds for a host
+// program that embeds this library next to such an allocator and owns no pool of its own, and for code
+// that runs where a cudaMalloc is unwelcome because it synchronises the whole device (inside a step
+// that is being timed or overlapped with a copy stream).
+//
+// For them the work area lives inside the library image: the file-scope array below, 296 x 4096 floats
+// (4 849 664 bytes).  Every GPU that loads libftl_b200.so carries that array from load until the process
+// exits, whether or not this entry point is ever called.  296 is the largest number of partial rows the
+// backward ever uses (two CTAs per SM on 148 SMs); 4096 is the model width of the flagship
+// configuration.  Requests that need more (dim > 4096) are refused with cudaErrorInvalidValue and a
+// message readable through ftl_last_error(); use ftl_rmsnorm_bwd() with your own scratch for those.
+//
+// Things a caller must know:
+//  * The name `g_rmsnorm_static_scratch` is only a handle on the host side.  The device address is looked
+//    up once per device with cudaGetSymbolAddress, with that device current, by the first call made on
+//    that device.  Make that first call outside of any stream capture; later calls only launch kernels.
+//  * No cudaMalloc, cudaFree or other allocating routine is called, on the first call or later.
+//  * All calls on one GPU share the one array, and it keeps whatever the previous call left in it.  Nothing
+//    has to be cleared between calls: each call writes every partial row it later folds before it reads
+//    it.  For the same reason two calls whose kernels can overlap on the GPU (different streams, no
+//    dependency between them) race on the array and produce garbage — order them on one stream or with
+//    an event.
+constexpr int kStaticScratchRows = 2 * ftl::kNumSMs;   // 296
+constexpr int kStaticScratchDim = 4096;
+static __device__ __align__(256) float g_rmsnorm_static_scratch[kStaticScratchRows * kStaticScratchDim];
+
+constexpr int kMaxDevices = 64;
+static float* g_static_scratch_ptr[kMaxDevices] = {nullptr};
+static thread_local char g_last_error[256] = "";
+
+FTL_API const char* ftl_last_error(void) { return g_last_error; }
+
+FTL_API int64_t ftl_rmsnorm_bwd_static_capacity(void) {
+    return (int64_t)kStaticScratchRows * kStaticScratchDim * (int64_t)sizeof(float);
+}
+
+FTL_API int ftl_rmsnorm_bwd_static(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                                   void* dx, void* dw, int rows, int dim, cudaStream_t stream) {
+    g_last_error[0] = 0;
+    if (rows <= 0 || dim <= 0 || dim % 8) {
+        snprintf(g_last_error, sizeof g_last_error, "ftl_rmsnorm_bwd_static: rows=%d dim=%d: dim must be a positive multiple of 8", rows, dim);
+        return (int)cudaErrorInvalidValue;
+    }
+    const int parts = ftl_rmsnorm_partials(rows);
+    if (dim > kStaticScratchDim || (int64_t)parts * dim > (int64_t)kStaticScratchRows * kStaticScratchDim) {
+        snprintf(g_last_error, sizeof g_last_error,
+                 "ftl_rmsnorm_bwd_static: dim=%d needs %lld scratch bytes, the built-in area holds %lld (dim <= %d); "
+                 "call ftl_rmsnorm_bwd with caller-provided scratch instead",
+                 dim, (long long)parts * dim * 4, (long long)ftl_rmsnorm_bwd_static_capacity(), kStaticScratchDim);
+        return (int)cudaErrorInvalidValue;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        snprintf(g_last_error, sizeof g_last_error, "ftl_rmsnorm_bwd_static: cudaGetDevice failed (%d), device %d", (int)e, dev);
+        return e != cudaSuccess ? (int)e : (int)cudaErrorInvalidDevice;
+    }
+    float* scratch = g_static_scratch_ptr[dev];
+    if (scratch == nullptr) {
+        // once per device, with that device current: turn the host-side symbol into this device's address
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_rmsnorm_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            snprintf(g_last_error, sizeof g_last_error, "ftl_rmsnorm_bwd_static: cudaGetSymbolAddress failed: %s",
+                     cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : (int)cudaErrorInvalidSymbol;
+        }
+        scratch = static_cast<float*>(p);
+        g_static_scratch_ptr[dev] = scratch;
+    }
+    int threads = norm_threads(dim);
+    if (threads > 256) threads = 256;
+    auto DY = (const __nv_bfloat16*)dy; auto X = (const __nv_bfloat16*)x; auto W = (const __nv_bfloat16*)w;
+    auto DR = (const __nv_bfloat16*)dres; auto DX = (__nv_bfloat16*)dx;
+    if (dres) rmsnorm_bwd_kernel<true><<<parts, threads, 0, stream>>>(DY, X, W, rstd, DR, DX, scratch, rows, dim);
+    else rmsnorm_bwd_kernel<false><<<parts, threads, 0, stream>>>(DY, X, W, rstd, nullptr, DX, scratch, rows, dim);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) {
+        rmsnorm_dw_finalize_kernel<<<(dim + 255) / 256, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw);
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) snprintf(g_last_error, sizeof g_last_error, "ftl_rmsnorm_bwd_static: launch failed: %s", cudaGetErrorString(e));
+    return (int)e;
 }

@@ -28,6 +28,18 @@ int ftl_rmsnorm_partials(int rows);
 int ftl_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
                     void* dx, void* dw, float* scratch, int rows, int dim, ftl_stream_t stream);
 
+/* Same backward, for callers that cannot supply scratch (no counterpart in the reference, which has no
+ * native code and lets PyTorch allocate).  Meant for the recovery path after a CUDA out-of-memory error and
+ * for host programs that sit next to a caching allocator owning the whole device: there every cudaMalloc
+ * fails, so the work area is a 4 849 664-byte array inside the library image (held by each GPU that loads
+ * the library until exit).  Limit: dim <= 4096; larger requests return cudaErrorInvalidValue and set
+ * ftl_last_error().  Allocates nothing.  The first call on each device resolves the array's device address
+ * (do it outside stream capture).  Calls share the array: calls that may overlap on one GPU race. */
+int ftl_rmsnorm_bwd_static(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                           void* dx, void* dw, int rows, int dim, ftl_stream_t stream);
+int64_t ftl_rmsnorm_bwd_static_capacity(void);   /* bytes of the built-in work area */
+const char* ftl_last_error(void);                /* message of the last refused call on this thread ("" if none) */
+
 /* ---- RoPE, in place on the q|k column block of a fused qkv buffer — reference: model.py:100-126 ---- */
 int ftl_rope_inplace(void* qkv, const float* cos_t, const float* sin_t, int64_t tokens, int seq_len,
                      int row_stride, int rot_cols, int head_dim, int inverse, ftl_stream_t stream);
