@@ -1,0 +1,373 @@
+// bf16 GEMM on the 5th-generation tensor cores: TMA -> 128B-swizzled shared memory ->
+// tcgen05.mma (one elected thread) -> fp32 accumulators in TMEM -> tcgen05.ld -> fused epilogue -> global.
+//
+//   C[M, N] = sum_r A(m, r) * B(n, r)
+//
+// A and B are each either "K-major" (reduction index contiguous: x @ W^T, the forward Linear of
+// /root/reference/model.py:195, 215, 254, 379) or "MN-major" (output index contiguous: the operand is the
+// transpose of a row-major matrix, which is what autograd's dgrad dY @ W and wgrad dY^T @ X need), so the
+// three GEMM flavours of a training step run through one kernel without transposing anything in memory.
+// The reduction may be split over two (A, B) pairs (kb < nk1 reads pair 1, the rest pair 2), which turns
+// d(hn) = dgate @ W1 + dup @ W3 into a single GEMM over K = 2 x 14336 with no accumulate pass.
+//
+// Fused epilogues:
+//   EPI_PLAIN   bf16 store.
+//   EPI_SWIGLU  B tile = 128 rows of w1 | 128 rows of w3 (two TMA boxes, one N=256 MMA); the epilogue
+//               writes gate, up (bf16, saved for backward) and act = bf16(bf16(silu(gate)) * up)  (K9+K10).
+//   EPI_ROPE    rotary embedding on the q|k columns of the fused QKV projection (K3+K4): the accumulator
+//               is rounded to bf16 (the Linear's output dtype), adjacent pairs are rotated in fp32 with
+//               the interleaved convention of model.py:121-126, and rounded once more.
+//
+// Structure: persistent, one CTA per SM, 192 threads: warp 0 = TMA producer, warp 1 = TMEM owner + MMA
+// issuer, warps 2-5 = epilogue (warp w may only touch TMEM lanes 32*(w%4)..+31).  4-stage smem ring
+// (48 KB per stage: A 128x64, B 256x64), 2 accumulator stages of 256 TMEM columns each, so the epilogue of
+// tile i overlaps the MMAs of tile i+1.  Tiles are walked M-fastest, so the CTAs running at the same time
+// share a B (weight) tile through L2 and the weight matrix streams from HBM exactly once.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cudaTypedefs.h>
+
+#include <mutex>
+
+#include "common/ptx.cuh"
+#include "common/util.cuh"
+
+namespace ftl {
+
+constexpr int BM = 128, BN = 256, BK = 64, kStages = 4, kAccStages = 2;
+constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
+constexpr int kGemmThreads = 192;
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+
+enum { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_ROPE = 2 };
+
+struct GemmArgs {
+    __nv_bfloat16* C;       // PLAIN/ROPE: [M, N]; SWIGLU: act [M, N/2]
+    __nv_bfloat16* C_gate;  // SWIGLU: raw gate / up outputs (may be null)
+    __nv_bfloat16* C_up;
+    const float* cos_t;     // ROPE: fp32 [seq_len, head_dim/2]
+    const float* sin_t;
+    int64_t ldc;
+    int M, N, K;            // N counts accumulator columns (SWIGLU: 2 x hidden)
+    int nk1;                // k-blocks served by the first (A, B) pair; the rest come from the second
+    int seq_len, head_dim, rot_cols;
+};
+
+template <int kEpi, bool kAMn, bool kBMn>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+               const GemmArgs g) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+    uint64_t* full = bars;                       // [kStages]     TMA -> MMA
+    uint64_t* empty = bars + kStages;            // [kStages]     MMA -> TMA
+    uint64_t* acc_full = bars + 2 * kStages;     // [kAccStages]  MMA -> epilogue
+    uint64_t* acc_empty = acc_full + kAccStages; // [kAccStages]  epilogue -> MMA
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + kAccStages);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m_tiles = (g.M + BM - 1) / BM;
+    const int n_tiles = (g.N + BN - 1) / BN;
+    const int num_tiles = m_tiles * n_tiles;
+    const int num_kb = (g.K + BK - 1) / BK;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmB);
+        for (int i = 0; i < kStages; ++i) {
+            ptx::mbar_init(&full[i], 1);
+            ptx::mbar_init(&empty[i], 1);
+        }
+        for (int i = 0; i < kAccStages; ++i) {
+            ptx::mbar_init(&acc_full[i], 1);
+            ptx::mbar_init(&acc_empty[i], 4);  // one arrive per epilogue warp
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        if (ptx::elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile % m_tiles) * BM;
+                const int n_blk = tile / m_tiles;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    ptx::mbar_wait(&empty[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * kStageBytes;
+                    uint8_t* sb = sa + kABytes;
+                    ptx::mbar_arrive_expect_tx(&full[stage], kStageBytes);
+                    const bool second = kb >= g.nk1;
+                    const CUtensorMap* ma = second ? &tmA2 : &tmA;
+                    const CUtensorMap* mb = second ? &tmB2 : &tmB;
+                    const int r0 = (second ? kb - g.nk1 : kb) * BK;  // reduction coordinate
+                    if (!kAMn) {
+                        ptx::tma_load_2d(sa, ma, &full[stage], r0, m0);                 // box {64 r, 128 m}
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j)                               // boxes {64 m, 64 r}
+                            ptx::tma_load_2d(sa + j * (64 * BK * 2), ma, &full[stage], m0 + j * 64, r0);
+                    }
+                    if (kEpi == EPI_SWIGLU) {
+                        // rows [0,128) of the B tile from w1, rows [128,256) from w3 (same row range of each)
+                        ptx::tma_load_2d(sb, &tmB, &full[stage], r0, n_blk * (BN / 2));
+                        ptx::tma_load_2d(sb + kBBytes / 2, &tmB2, &full[stage], r0, n_blk * (BN / 2));
+                    } else if (!kBMn) {
+                        ptx::tma_load_2d(sb, mb, &full[stage], r0, n_blk * BN);         // box {64 r, 256 n}
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)                               // boxes {64 n, 64 r}
+                            ptx::tma_load_2d(sb + j * (64 * BK * 2), mb, &full[stage], n_blk * BN + j * 64, r0);
+                    }
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, kAMn, kBMn);
+        // K-major, 128B swizzle: 8-row groups are 1024 B apart (SBO); LBO unused.
+        // MN-major, 128B swizzle: 64-element (128 B) columns blocks are one TMA box apart (LBO = 64 r x 128 B),
+        // 8-row reduction groups 1024 B apart (SBO).
+        constexpr uint32_t kLboMn = 64 * BK * 2, kSbo = 1024;
+        int stage = 0, acc = 0;
+        uint32_t phase = 0, acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            ptx::mbar_wait(&acc_empty[acc], acc_phase ^ 1);
+            ptx::tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * BN;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                ptx::mbar_wait(&full[stage], phase);
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) {
+                    const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes);
+                    const uint32_t sb = sa + kABytes;
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        // one UMMA consumes 16 reduction elements: 32 B inside the swizzle row (K-major) or
+                        // 16 rows of 128 B (MN-major)
+                        const uint64_t da = kAMn ? ptx::umma_smem_desc(sa + k * 16 * 128, kLboMn, kSbo)
+                                                 : ptx::umma_smem_desc(sa + k * 32, 0, kSbo);
+                        const uint64_t db = kBMn ? ptx::umma_smem_desc(sb + k * 16 * 128, kLboMn, kSbo)
+                                                 : ptx::umma_smem_desc(sb + k * 32, 0, kSbo);
+                        ptx::umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0);
+                    }
+                    ptx::umma_commit(&empty[stage]);                       // frees the smem slot when the MMAs retire
+                    if (kb == num_kb - 1) ptx::umma_commit(&acc_full[acc]);  // accumulator ready
+                }
+                __syncwarp();
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+    } else {
+        // ================= epilogue: TMEM -> registers -> global =================
+        const int q = warp & 3;                 // TMEM lane quarter this warp may read
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0 = (tile % m_tiles) * BM;
+            const int n_blk = tile / m_tiles;
+            const int row = m0 + q * 32 + lane;
+            ptx::mbar_wait(&acc_full[acc], acc_phase);
+            ptx::tc_fence_after();
+            const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
+            if (kEpi == EPI_SWIGLU) {
+                const int h0 = n_blk * (BN / 2);   // first hidden column of this tile
+                const int hidden = g.N / 2;
+#pragma unroll 1
+                for (int c = 0; c < BN / 2; c += 32) {
+                    uint32_t rg[32], ru[32];
+                    ptx::tmem_ld32(taddr + c, rg);
+                    ptx::tmem_ld32(taddr + BN / 2 + c, ru);
+                    ptx::tmem_ld_wait();
+                    if (row < g.M) {
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) {
+                            const int col = h0 + c + v * 8;
+                            if (col < hidden) {
+                                float gt[8], up[8], act[8];
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) {
+                                    gt[j] = round_bf16(__uint_as_float(rg[v * 8 + j]));
+                                    up[j] = round_bf16(__uint_as_float(ru[v * 8 + j]));
+                                    act[j] = round_bf16(gt[j] / (1.f + __expf(-gt[j]))) * up[j];
+                                }
+                                const int64_t off = (int64_t)row * g.ldc + col;
+                                st8(g.C + off, pack8(act));
+                                if (g.C_gate) st8(g.C_gate + off, pack8(gt));
+                                if (g.C_up) st8(g.C_up + off, pack8(up));
+                            }
+                        }
+                    }
+                }
+            } else {
+                const int n0 = n_blk * BN;
+#pragma unroll 1
+                for (int c = 0; c < BN; c += 32) {
+                    uint32_t r[32];
+                    ptx::tmem_ld32(taddr + c, r);
+                    ptx::tmem_ld_wait();
+                    if (row < g.M) {
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) {
+                            const int col = n0 + c + v * 8;
+                            if (col < g.N) {
+                                float f[8];
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
+                                if (kEpi == EPI_ROPE && col < g.rot_cols) {
+                                    const int pos = row % g.seq_len;
+                                    const int pair0 = (col % g.head_dim) >> 1;
+                                    const int64_t to = (int64_t)pos * (g.head_dim >> 1) + pair0;
+                                    const float4 cs = *reinterpret_cast<const float4*>(g.cos_t + to);
+                                    const float4 sn = *reinterpret_cast<const float4*>(g.sin_t + to);
+                                    const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
+#pragma unroll
+                                    for (int j = 0; j < 4; ++j) {
+                                        const float a = round_bf16(f[2 * j]), b = round_bf16(f[2 * j + 1]);
+                                        f[2 * j] = a * cc[j] - b * ss[j];
+                                        f[2 * j + 1] = a * ss[j] + b * cc[j];
+                                    }
+                                }
+                                st8(g.C + (int64_t)row * g.ldc + col, pack8(f));
+                            }
+                        }
+                    }
+                }
+            }
+            // every TMEM read of this accumulator stage has completed (wait::ld above): hand it back
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&acc_empty[acc]);
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------ host
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+static std::once_flag g_encode_once;
+
+static void load_encode() {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+        g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+}
+
+// Row-major bf16 matrix [rows, cols] (leading dimension ld elements); box = {box_cols (contiguous), box_rows}.
+static int make_tmap(CUtensorMap* out, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_cols,
+                     int box_rows) {
+    std::call_once(g_encode_once, load_encode);
+    if (!g_encode) return (int)cudaErrorNotSupported;
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
+template <int kEpi, bool kAMn, bool kBMn>
+static int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2, const CUtensorMap& b2,
+                  const GemmArgs& g, int max_ctas, cudaStream_t stream) {
+    auto kern = gemm_tc_kernel<kEpi, kAMn, kBMn>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const int tiles = ((g.M + BM - 1) / BM) * ((g.N + BN - 1) / BN);
+    int grid = max_ctas > 0 ? max_ctas : kNumSMs;
+    if (grid > tiles) grid = tiles;
+    kern<<<grid, kGemmThreads, kSmemBytes, stream>>>(a, b, a2, b2, g);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace ftl
+
+using namespace ftl;
+
+// C[M,N] = A·B with a, b row-major bf16 matrices and `a_mn` / `b_mn` selecting how they are read:
+//   a_mn = 0: a is [M, K] (lda);  a_mn = 1: a is [K, M] (lda)  — i.e. C = a^T ...
+//   b_mn = 0: b is [N, K] (ldb);  b_mn = 1: b is [K, N] (ldb)
+// Optional second reduction segment (a2, b2, K2): C = A·B + A2·B2.  max_ctas = 0 uses all 148 SMs.
+FTL_API int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c,
+                          int64_t ldc, int M, int N, int K, const void* a2, int64_t lda2, const void* b2, int64_t ldb2,
+                          int K2, int max_ctas, cudaStream_t stream) {
+    if (M <= 0 || N <= 0 || K <= 0 || (N % 8) || (ldc % 8) || (lda % 8) || (ldb % 8) || (K % BK && K2 > 0))
+        return (int)cudaErrorInvalidValue;
+    CUtensorMap ta, tb, ta2, tb2;
+    int e;
+    e = a_mn ? make_tmap(&ta, a, K, M, lda, 64, BK) : make_tmap(&ta, a, M, K, lda, BK, BM);
+    if (e) return e;
+    e = b_mn ? make_tmap(&tb, b, K, N, ldb, 64, BK) : make_tmap(&tb, b, N, K, ldb, BK, BN);
+    if (e) return e;
+    ta2 = ta;
+    tb2 = tb;
+    if (K2 > 0) {
+        e = a_mn ? make_tmap(&ta2, a2, K2, M, lda2, 64, BK) : make_tmap(&ta2, a2, M, K2, lda2, BK, BM);
+        if (e) return e;
+        e = b_mn ? make_tmap(&tb2, b2, K2, N, ldb2, 64, BK) : make_tmap(&tb2, b2, N, K2, ldb2, BK, BN);
+        if (e) return e;
+    }
+    GemmArgs g{};
+    g.C = (__nv_bfloat16*)c;
+    g.ldc = ldc;
+    g.M = M; g.N = N; g.K = K + (K2 > 0 ? K2 : 0);
+    g.nk1 = (K + BK - 1) / BK;
+    if (!a_mn && !b_mn) return launch<EPI_PLAIN, false, false>(ta, tb, ta2, tb2, g, max_ctas, stream);
+    if (!a_mn && b_mn) return launch<EPI_PLAIN, false, true>(ta, tb, ta2, tb2, g, max_ctas, stream);
+    if (a_mn && b_mn) return launch<EPI_PLAIN, true, true>(ta, tb, ta2, tb2, g, max_ctas, stream);
+    return launch<EPI_PLAIN, true, false>(ta, tb, ta2, tb2, g, max_ctas, stream);
+}
+
+// gate|up dual GEMM with the SwiGLU epilogue: x [M, K], w1 / w3 [H, K]; writes act (and gate, up if non-null), [M, H].
+FTL_API int ftl_gemm_swiglu(const void* x, int64_t ldx, const void* w1, const void* w3, int64_t ldw, void* act,
+                            void* gate, void* up, int64_t ldo, int M, int H, int K, int max_ctas, cudaStream_t stream) {
+    if (M <= 0 || H <= 0 || K <= 0 || (H % 8) || (ldo % 8) || (ldx % 8) || (ldw % 8)) return (int)cudaErrorInvalidValue;
+    CUtensorMap ta, tb, tb2;
+    int e;
+    if ((e = make_tmap(&ta, x, M, K, ldx, BK, BM))) return e;
+    if ((e = make_tmap(&tb, w1, H, K, ldw, BK, BN / 2))) return e;
+    if ((e = make_tmap(&tb2, w3, H, K, ldw, BK, BN / 2))) return e;
+    GemmArgs g{};
+    g.C = (__nv_bfloat16*)act; g.C_gate = (__nv_bfloat16*)gate; g.C_up = (__nv_bfloat16*)up;
+    g.ldc = ldo;
+    g.M = M; g.N = 2 * H; g.K = K;   // accumulator columns: 128 gate + 128 up per tile; ceil(2H/256) = ceil(H/128) tiles
+    g.nk1 = (K + BK - 1) / BK;
+    return launch<EPI_SWIGLU, false, false>(ta, tb, ta, tb2, g, max_ctas, stream);
+}
+
+// fused QKV projection + RoPE on the first rot_cols output columns (q heads then k heads).
+FTL_API int ftl_gemm_qkv_rope(const void* x, int64_t ldx, const void* wqkv, int64_t ldw, void* qkv, int64_t ldo,
+                              const float* cos_t, const float* sin_t, int M, int N, int K, int seq_len, int head_dim,
+                              int rot_cols, int max_ctas, cudaStream_t stream) {
+    if (M <= 0 || N <= 0 || K <= 0 || (N % 8) || (ldo % 8) || (ldx % 8) || (ldw % 8) || (head_dim % 8) || (rot_cols % 8))
+        return (int)cudaErrorInvalidValue;
+    CUtensorMap ta, tb;
+    int e;
+    if ((e = make_tmap(&ta, x, M, K, ldx, BK, BM))) return e;
+    if ((e = make_tmap(&tb, wqkv, N, K, ldw, BK, BN))) return e;
+    GemmArgs g{};
+    g.C = (__nv_bfloat16*)qkv; g.ldc = ldo;
+    g.M = M; g.N = N; g.K = K; g.nk1 = (K + BK - 1) / BK;
+    g.cos_t = cos_t; g.sin_t = sin_t; g.seq_len = seq_len; g.head_dim = head_dim; g.rot_cols = rot_cols;
+    return launch<EPI_ROPE, false, false>(ta, tb, ta, tb, g, max_ctas, stream);
+}

@@ -56,6 +56,9 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_grad_norm_partials", [])
     _sig(L, "ftl_grad_norm", [P, I64, P, P, P, I, P])
     _sig(L, "ftl_adamw_step", [P, P, P, P, I64, P, P, P])
+    _sig(L, "ftl_gemm_bf16", [P, I64, I, P, I64, I, P, I64, I, I, I, P, I64, P, I64, I, I, P])
+    _sig(L, "ftl_gemm_swiglu", [P, I64, P, P, I64, P, P, P, I64, I, I, I, I, P])
+    _sig(L, "ftl_gemm_qkv_rope", [P, I64, P, I64, P, I64, P, P, I, I, I, I, I, I, I, P])
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -174,3 +177,54 @@ def adamw_step(p, g, m, v, hyper, stats=None):
     _bf16(p, g, m, v)
     _check(lib().ftl_adamw_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), _ptr(hyper), _ptr(stats), _stream()),
            "ftl_adamw_step")
+
+
+# ---- tcgen05 GEMMs (csrc/gemm_tc.cu) ---------------------------------------------------------------
+def _mat(t):
+    assert t.is_cuda and t.dtype == torch.bfloat16 and t.dim() == 2 and t.stride(1) == 1, (t.dtype, t.shape, t.stride())
+    return t
+
+
+def gemm(a, b, out, a_mn=False, b_mn=False, a2=None, b2=None, max_ctas=0):
+    """out[M, N] = A . B^T-style product on the tcgen05 path.
+
+    a_mn=False: a is [M, K];  a_mn=True: a is [K, M] (A = a^T).
+    b_mn=False: b is [N, K];  b_mn=True: b is [K, N].
+    Optional second reduction segment (a2, b2) is added: out = A.B + A2.B2."""
+    _mat(a), _mat(b), _mat(out)
+    M, N = out.shape
+    K = a.shape[0] if a_mn else a.shape[1]
+    assert (a.shape[1] if a_mn else a.shape[0]) == M and (b.shape[1] if b_mn else b.shape[0]) == N
+    assert (b.shape[0] if b_mn else b.shape[1]) == K
+    K2 = 0
+    if a2 is not None:
+        _mat(a2), _mat(b2)
+        K2 = a2.shape[0] if a_mn else a2.shape[1]
+    _check(lib().ftl_gemm_bf16(_ptr(a), a.stride(0), int(a_mn), _ptr(b), b.stride(0), int(b_mn), _ptr(out),
+                               out.stride(0), M, N, K, _ptr(a2), a2.stride(0) if a2 is not None else 0, _ptr(b2),
+                               b2.stride(0) if b2 is not None else 0, K2, max_ctas, _stream()), "ftl_gemm_bf16")
+    return out
+
+
+def gemm_swiglu(x, w1, w3, act, gate=None, up=None, max_ctas=0):
+    """act = silu(x @ w1^T) * (x @ w3^T) in one kernel; optionally also stores the two pre-activations."""
+    _mat(x), _mat(w1), _mat(w3), _mat(act)
+    M, K = x.shape
+    H = w1.shape[0]
+    assert w1.stride(0) == w3.stride(0) and act.shape == (M, H)
+    for t in (gate, up):
+        assert t is None or (t.shape == act.shape and t.stride(0) == act.stride(0))
+    _check(lib().ftl_gemm_swiglu(_ptr(x), x.stride(0), _ptr(w1), _ptr(w3), w1.stride(0), _ptr(act), _ptr(gate), _ptr(up),
+                                 act.stride(0), M, H, K, max_ctas, _stream()), "ftl_gemm_swiglu")
+    return act
+
+
+def gemm_qkv_rope(x, wqkv, qkv, cos, sin, seq_len, head_dim, rot_cols, max_ctas=0):
+    """qkv = x @ wqkv^T with RoPE applied to the first rot_cols columns (q heads then k heads) in the epilogue."""
+    _mat(x), _mat(wqkv), _mat(qkv)
+    M, K = x.shape
+    Nq = wqkv.shape[0]
+    _check(lib().ftl_gemm_qkv_rope(_ptr(x), x.stride(0), _ptr(wqkv), wqkv.stride(0), _ptr(qkv), qkv.stride(0), _ptr(cos),
+                                   _ptr(sin), M, Nq, K, seq_len, head_dim, rot_cols, max_ctas, _stream()),
+           "ftl_gemm_qkv_rope")
+    return qkv

@@ -155,3 +155,53 @@ def test_grad_norm_and_adamw_match_torch(N):
     N.grad_norm(g2, hyper, scratch, stats, clip=True)
     N.adamw_step(p, g2, m, v, hyper, stats)
     assert float(stats[2]) == 0.0 and torch.equal(p, before)
+
+
+# ---- tcgen05 GEMMs (csrc/gemm_tc.cu): every operand-major combination and fused epilogue vs fp32 matmul ----
+def _rel(out, ref):
+    return float((out.float() - ref).norm() / ref.norm())
+
+
+@pytest.mark.parametrize("M,Nn,K", [(256, 512, 256), (200, 344, 136), (2048, 1024, 4096)])
+def test_gemm_tc_nt(N, M, Nn, K):
+    a, b = bf(M, K, scale=0.5, seed=1), bf(Nn, K, scale=0.5, seed=2)
+    out = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+    N.gemm(a, b, out)
+    assert _rel(out, a.float() @ b.float().t()) < 5e-3
+
+
+def test_gemm_tc_dgrad_wgrad_and_split_reduction(N):
+    M, Nn, K = 384, 512, 320
+    dy, w, x = bf(M, Nn, scale=0.5, seed=1), bf(Nn, K, scale=0.5, seed=2), bf(M, K, scale=0.5, seed=3)
+    dx = torch.empty(M, K, device=DEV, dtype=torch.bfloat16)
+    N.gemm(dy, w, dx, b_mn=True)                       # dgrad: dY @ W
+    assert _rel(dx, dy.float() @ w.float()) < 5e-3
+    dw = torch.empty(Nn, K, device=DEV, dtype=torch.bfloat16)
+    N.gemm(dy, x, dw, a_mn=True, b_mn=True)            # wgrad: dY^T @ X
+    assert _rel(dw, dy.float().t() @ x.float()) < 5e-3
+    dy2, w2 = bf(M, Nn, scale=0.5, seed=4), bf(Nn, K, scale=0.5, seed=5)
+    N.gemm(dy, w, dx, b_mn=True, a2=dy2, b2=w2)        # dY @ W + dY2 @ W2 in one pass
+    assert _rel(dx, dy.float() @ w.float() + dy2.float() @ w2.float()) < 5e-3
+
+
+def test_gemm_tc_swiglu_epilogue(N):
+    M, H, K = 256, 384, 256
+    x, w1, w3 = bf(M, K, scale=0.5, seed=1), bf(H, K, scale=0.1, seed=2), bf(H, K, scale=0.1, seed=3)
+    act, gate, up = (torch.empty(M, H, device=DEV, dtype=torch.bfloat16) for _ in range(3))
+    N.gemm_swiglu(x, w1, w3, act, gate, up)
+    g, u = x.float() @ w1.float().t(), x.float() @ w3.float().t()
+    assert _rel(gate, g) < 5e-3 and _rel(up, u) < 5e-3
+    assert _rel(act, torch.nn.functional.silu(g) * u) < 1e-2
+
+
+def test_gemm_tc_qkv_rope_epilogue(N):
+    B, S, H, KV, hd, K = 2, 128, 4, 2, 64, 256
+    M, Nq, rot = B * S, (H + 2 * KV) * hd, (H + KV) * hd
+    x, w = bf(M, K, scale=0.5, seed=1), bf(Nq, K, scale=0.1, seed=2)
+    cos, sin = T.rope_table(hd, S, 500000.0, device=DEV)
+    out = torch.empty(M, Nq, device=DEV, dtype=torch.bfloat16)
+    N.gemm_qkv_rope(x, w, out, cos, sin, S, hd, rot)
+    ref = (x.float() @ w.float().t()).to(torch.bfloat16)
+    ref_rot = T.rope_apply(ref[:, :rot].reshape(B, S, H + KV, hd), cos, sin).reshape(M, rot)
+    assert _rel(out[:, :rot], ref_rot.float()) < 5e-3
+    assert _rel(out[:, rot:], ref[:, rot:].float()) < 5e-3
