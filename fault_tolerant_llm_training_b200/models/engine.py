@@ -34,12 +34,16 @@ from .llama import Transformer, build_model, flat_size, param_layout
 class FlatState:
     """Flat bf16 buffers for params / grads / exp_avg / exp_avg_sq with the model's tensors as views."""
 
-    def __init__(self, model: Transformer, device: torch.device, allocator=None):
+    def __init__(self, model: Transformer, device: torch.device, buffers=None, pad_to: int = 128):
+        """buffers: optional dict name -> callable(numel) returning a zeroed bf16 tensor for "p" / "g" / "m" / "v"
+        (the data-parallel engine puts p and g in peer-mapped memory); pad_to rounds the flat length up so it
+        splits evenly into per-rank shards."""
         self.layout = param_layout(model)
-        self.numel = flat_size(self.layout)
-        alloc = allocator or (lambda n: torch.zeros(n, dtype=torch.bfloat16, device=device))
-        self.p, self.g = alloc(self.numel), alloc(self.numel)
-        self.m, self.v = alloc(self.numel), alloc(self.numel)
+        self.numel = (flat_size(self.layout) + pad_to - 1) // pad_to * pad_to
+        default = lambda n: torch.zeros(n, dtype=torch.bfloat16, device=device)
+        buffers = buffers or {}
+        self.p, self.g = buffers.get("p", default)(self.numel), buffers.get("g", default)(self.numel)
+        self.m, self.v = buffers.get("m", default)(self.numel), buffers.get("v", default)(self.numel)
         self.index = {}
         params = dict(model.named_parameters())
         with torch.no_grad():
@@ -348,15 +352,15 @@ class NativeTrainer:
         self.hyper = torch.zeros(8, dtype=torch.float32, device=self.device)
         self.stats = torch.zeros(4, dtype=torch.float32, device=self.device)
         self.gn_scratch = torch.zeros(N.grad_norm_partials(), dtype=torch.float32, device=self.device)
-        self.result_dev = torch.zeros(4, dtype=torch.float32, device=self.device)
-        self.result_host = [torch.zeros(4, dtype=torch.float32).pin_memory() for _ in range(self.RING)]
+        self.result_dev = torch.zeros(8, dtype=torch.float32, device=self.device)
+        self.result_host = [torch.zeros(8, dtype=torch.float32).pin_memory() for _ in range(self.RING)]
         self.events = [torch.cuda.Event() for _ in range(self.RING)]
         self._slot = 0
         self._stage = None
         self._pending: List[LossHandle] = []   # results not yet inspected by the host (at most 2)
         self.last_grad_norm = 0.0
         self.h2d_bytes_per_step = 0
-        self.d2h_bytes_per_step = 16
+        self.d2h_bytes_per_step = 32
         self.kernel_launches_per_step = 0
 
     def _make_flat_state(self) -> FlatState:
@@ -396,10 +400,7 @@ class NativeTrainer:
         # gradient norm made that step's update a no-op on the device (csrc/optim.cu), so raising late
         # still checkpoints clean state (reference: get_total_norm(error_if_nonfinite=True), utils.py:61)
         while len(self._pending) >= 2:
-            old = self._pending.pop(0)
-            if not old.finite():
-                raise FloatingPointError("The total norm of gradients is non-finite, so it cannot be clipped.")
-            self.last_grad_norm = old.grad_norm()
+            self._inspect(self._pending.pop(0))
         n_items = self._global_token_count(int(labels.ne(-100).sum()))
         slot = self._slot
         self._slot = (slot + 1) % self.RING
@@ -414,15 +415,34 @@ class NativeTrainer:
         self.engine.backward(st["tok_d"])
         self._reduce_and_update(hyper, loss)
         self.lr_scheduler.step()
-        # result: loss, grad norm, clip coef, finite
+        # result: loss, grad norm, clip coef, finite, comm status
         self.result_dev[0:1].copy_(loss)
         self.result_dev[1:4].copy_(self.stats[0:3])
+        self._write_status(self.result_dev[4:5])
         self.result_host[slot].copy_(self.result_dev, non_blocking=True)  # the one D2H copy of the step
         self.events[slot].record()
         handle = LossHandle(self.result_host[slot], self.events[slot])
         self._pending.append(handle)
         self.kernel_launches_per_step = N.LAUNCHES - launches0
         return handle
+
+    def _inspect(self, old: "LossHandle") -> None:
+        """Host-side check of a finished step (two steps late, see step())."""
+        old.event.synchronize()
+        if old.host[4] != 0.0:
+            from ..ft.signals import PeerAbort
+            raise PeerAbort(f"collective step aborted (status {int(old.host[4])}: 1 = barrier timeout, 2 = peer abort)")
+        if not old.finite():
+            raise FloatingPointError("The total norm of gradients is non-finite, so it cannot be clipped.")
+        self.last_grad_norm = old.grad_norm()
+
+    def _write_status(self, dst: torch.Tensor) -> None:
+        dst.zero_()
+
+    def drain(self) -> None:
+        """Inspect every outstanding step result (called before a checkpoint is taken)."""
+        while self._pending:
+            self._inspect(self._pending.pop(0))
 
     def _reduce_and_update(self, hyper: torch.Tensor, loss: torch.Tensor) -> None:
         """Single-GPU: grad norm over the flat gradient, then the fused AdamW pass."""

@@ -59,6 +59,21 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_gemm_bf16", [P, I64, I, P, I64, I, P, I64, I, I, I, P, I64, P, I64, I, I, P])
     _sig(L, "ftl_gemm_swiglu", [P, I64, P, P, I64, P, P, P, I64, I, I, I, I, P])
     _sig(L, "ftl_gemm_qkv_rope", [P, I64, P, I64, P, I64, P, P, I, I, I, I, I, I, I, P])
+    PP = ctypes.POINTER(c_void_p)
+    _sig(L, "ftl_symm_alloc", [PP, I64])
+    _sig(L, "ftl_symm_free", [P])
+    _sig(L, "ftl_ipc_export", [P, ctypes.c_char_p])
+    _sig(L, "ftl_ipc_import", [ctypes.c_char_p, PP])
+    _sig(L, "ftl_ipc_close", [P])
+    _sig(L, "ftl_comm_max_ranks", [])
+    _sig(L, "ftl_comm_flag_words", [])
+    _sig(L, "ftl_barrier", [P, I, I, ctypes.c_uint32, P, I64, P])
+    _sig(L, "ftl_raise_abort", [P, I, P])
+    _sig(L, "ftl_dp_partials", [I])
+    _sig(L, "ftl_dp_reduce_scatter", [P, I, I, I64, I64, P, P, I, P])
+    _sig(L, "ftl_dp_publish", [P, I, P, P, I, I, P])
+    _sig(L, "ftl_dp_finalize", [P, I, P, P, P, I, P])
+    _sig(L, "ftl_dp_adamw_allgather", [P, P, P, P, I, I, I64, I64, P, P, P, I, P])
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -228,3 +243,61 @@ def gemm_qkv_rope(x, wqkv, qkv, cos, sin, seq_len, head_dim, rot_cols, max_ctas=
                                    _ptr(sin), M, Nq, K, seq_len, head_dim, rot_cols, max_ctas, _stream()),
            "ftl_gemm_qkv_rope")
     return qkv
+
+
+# ---- multi-GPU data plane (csrc/comm.cu) -------------------------------------------------------------
+def symm_alloc(nbytes: int) -> int:
+    out = c_void_p()
+    code = lib().ftl_symm_alloc(ctypes.byref(out), nbytes)
+    if code != 0:
+        raise NativeError(f"ftl_symm_alloc({nbytes}) failed with CUDA error {code}")
+    return out.value
+
+
+def ipc_export(ptr: int) -> bytes:
+    buf = ctypes.create_string_buffer(64)
+    code = lib().ftl_ipc_export(c_void_p(ptr), buf)
+    if code != 0:
+        raise NativeError(f"cudaIpcGetMemHandle failed with CUDA error {code}")
+    return buf.raw
+
+
+def ipc_import(handle: bytes) -> int:
+    out = c_void_p()
+    code = lib().ftl_ipc_import(handle, ctypes.byref(out))
+    if code != 0:
+        raise NativeError(f"cudaIpcOpenMemHandle failed with CUDA error {code}")
+    return out.value
+
+
+def barrier(peer_flags, rank, world, epoch, status, timeout_ms=120000):
+    _check(lib().ftl_barrier(_ptr(peer_flags), rank, world, epoch & 0xffffffff, _ptr(status), timeout_ms, _stream()),
+           "ftl_barrier")
+
+
+def raise_abort(peer_flags, world):
+    _check(lib().ftl_raise_abort(_ptr(peer_flags), world, _stream()), "ftl_raise_abort")
+
+
+def dp_partials(max_ctas=0) -> int:
+    return lib().ftl_dp_partials(max_ctas)
+
+
+def dp_reduce_scatter(peer_g, rank, world, lo, n, partial, status, max_ctas=0):
+    _check(lib().ftl_dp_reduce_scatter(_ptr(peer_g), rank, world, lo, n, _ptr(partial), _ptr(status), max_ctas, _stream()),
+           "ftl_dp_reduce_scatter")
+
+
+def dp_publish(partial, nparts, loss_local, peer_slots, rank, world):
+    _check(lib().ftl_dp_publish(_ptr(partial), nparts, _ptr(loss_local), _ptr(peer_slots), rank, world, _stream()),
+           "ftl_dp_publish")
+
+
+def dp_finalize(slots, world, hyper, stats, loss_out, clip=True):
+    _check(lib().ftl_dp_finalize(_ptr(slots), world, _ptr(hyper), _ptr(stats), _ptr(loss_out), int(clip), _stream()),
+           "ftl_dp_finalize")
+
+
+def dp_adamw_allgather(peer_p, g, m, v, rank, world, lo, n, hyper, stats, status, max_ctas=0):
+    _check(lib().ftl_dp_adamw_allgather(_ptr(peer_p), _ptr(g), _ptr(m), _ptr(v), rank, world, lo, n, _ptr(hyper),
+                                        _ptr(stats), _ptr(status), max_ctas, _stream()), "ftl_dp_adamw_allgather")

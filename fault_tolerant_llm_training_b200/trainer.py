@@ -100,6 +100,11 @@ def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: floa
     if env.device.type == "cuda" and not force_torch:
         from .models.engine import NativeTrainer  # imports the sm_100a extension; fails loudly if missing
 
+        if env.distributed and parallel == "none":
+            raise ValueError("--parallel none with WORLD_SIZE > 1: ranks would train unsynchronised copies")
+        if env.distributed:
+            from .parallel.dp import DPNativeTrainer as NativeTrainer  # noqa: F811 (dp; fsdp shares the engine)
+
         return NativeTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps,
                              grad_max_norm=grad_max_norm, clip_mode=clip_mode, seed=seed,
                              parallel=parallel, bucket_mb=bucket_mb, cuda_graph=cuda_graph)
