@@ -104,4 +104,10 @@ def save_checkpoint(checkpoint_path: str, jobid: str, model, optimizer, lr_sched
 def load_checkpoint(checkpoint_path: str, checkpoint_id: str) -> Dict[str, Any]:
     """torch.load to CPU (reference: train.py:22)."""
     path = checkpoint_file(checkpoint_path, checkpoint_id)
+    if not os.path.exists(path):
+        # a job killed while consolidating leaves only the (durable) shard directory: resume from it
+        from .sharded import MANIFEST, load_sharded, shard_dir
+        d = shard_dir(checkpoint_path, checkpoint_id)
+        if os.path.exists(os.path.join(d, MANIFEST)):
+            return load_sharded(d)
     return torch.load(path, map_location="cpu", weights_only=False)

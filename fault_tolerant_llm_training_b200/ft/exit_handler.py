@@ -39,7 +39,7 @@ def handle_exit(model, optimizer, lr_scheduler, training_step, checkpoint_path, 
                 *, data_state: Optional[dict] = None, rank: int = 0, world_size: int = 1,
                 save_fn: Optional[Callable[..., str]] = None, resubmit_cmd: str = "",
                 resume_id: str = "", made_progress: bool = True, flags=None,
-                extra: Optional[dict] = None) -> Optional[str]:
+                extra: Optional[dict] = None, finalize_fn: Optional[Callable[..., object]] = None) -> Optional[str]:
     """Same positional signature as the reference's handle_exit (utils.py:65).
 
     Keyword-only extensions: dataset position, rank info, a pluggable save
@@ -81,6 +81,10 @@ def handle_exit(model, optimizer, lr_scheduler, training_step, checkpoint_path, 
                 info(f"[EXIT HANDLER] Failed to requeue job {jid}.")
             else:
                 info("[EXIT HANDLER] sbatch requeued, new job will load the last checkpoint")
+        if saved_path is not None and finalize_fn is not None:
+            # work that may run after the job has been resubmitted (sharded engines consolidate the shards into
+            # the reference-layout file here); the checkpoint was already durable when save_fn returned
+            finalize_fn(logger=logger)
     else:
         info(f"[EXIT HANDLER] Unknown exit signal {type}, terminating.")
     return saved_path

@@ -336,7 +336,8 @@ class NativeTrainer:
 
     def __init__(self, cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
                  grad_max_norm: float, clip_mode: str = "clip", seed: int = 0, parallel: str = "none",
-                 bucket_mb: int = 512, cuda_graph: bool = False):
+                 bucket_mb: int = 512, cuda_graph: bool = False, keep_shards: bool = False,
+                 consolidate: bool = True):
         if dtype != torch.bfloat16:
             raise ValueError("the B200 engine is bf16-only (use --device cpu for other dtypes)")
         N.lib()  # fail loudly if the sm_100a library is missing
@@ -362,6 +363,8 @@ class NativeTrainer:
         self.h2d_bytes_per_step = 0
         self.d2h_bytes_per_step = 32
         self.kernel_launches_per_step = 0
+        from ..ckpt.sharded import FlatCheckpointer
+        self.checkpointer = FlatCheckpointer(self, keep_shards=keep_shards, consolidate=consolidate)
 
     def _make_flat_state(self) -> FlatState:
         return FlatState(self.model, self.device)
@@ -452,12 +455,42 @@ class NativeTrainer:
 
     # -- checkpoint plumbing ----------------------------------------------------------------------
     def load_state(self, ckpt: dict) -> None:
-        self.model.load_state_dict(ckpt["model"], strict=True)  # copies into the flat views
-        self.optimizer.load_state_dict(ckpt["optimizer"])
+        if "_sharded_dir" in ckpt:
+            self._load_sharded(ckpt)
+        else:
+            self.model.load_state_dict(ckpt["model"], strict=True)  # copies into the flat views
+            self.optimizer.load_state_dict(ckpt["optimizer"])
         self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
+        torch.cuda.synchronize()
+
+    def _moment_range(self):
+        """Flat range of exp_avg / exp_avg_sq this rank maintains."""
+        return 0, self.flat.numel
+
+    def _load_sharded(self, ckpt: dict) -> None:
+        """Shard files -> device, straight through the native reader (no CPU state_dict is ever built)."""
+        from ..ckpt.sharded import read_range_to_device
+        d, m, f = ckpt["_sharded_dir"], ckpt["_manifest"], self.flat
+        if [list(x[1]) for x in m["layout"]] != [list(s) for _, s, _, _ in f.layout]:
+            raise ValueError("checkpoint was written for a different model shape")
+        n_ck = m["flat_numel"]   # padding at the tail may differ with the world size; the payload does not
+        n = min(n_ck, f.numel)
+        read_range_to_device(d, m, "p", 0, n, f.p[:n])
+        lo, hi = self._moment_range()
+        hi = min(hi, n)
+        if lo < hi:
+            read_range_to_device(d, m, "m", lo, hi, f.m[lo:hi])
+            read_range_to_device(d, m, "v", lo, hi, f.v[lo:hi])
+        g = m["optimizer"]["param_groups"][0]
+        for k, v in g.items():
+            self.optimizer.param_groups[0][k] = tuple(v) if k == "betas" else v
+        self.optimizer.steps_done = int(m["optimizer"]["steps_done"])
 
     def save_fn(self):
-        return None
+        return self.checkpointer.save
+
+    def finalize_fn(self):
+        return self.checkpointer.finalize
 
     def loss_value(self, loss: LossHandle) -> float:
         v = loss.item()

@@ -74,6 +74,10 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_dp_publish", [P, I, P, P, I, I, P])
     _sig(L, "ftl_dp_finalize", [P, I, P, P, P, I, P])
     _sig(L, "ftl_dp_adamw_allgather", [P, P, P, P, I, I, I64, I64, P, P, P, I, P])
+    _sig(L, "ftl_ckpt_init", [I64])
+    _sig(L, "ftl_ckpt_write", [ctypes.c_char_p, I, P, P, P, I, I, P])
+    _sig(L, "ftl_ckpt_read", [ctypes.c_char_p, I, P, P, P, I, P])
+    _sig(L, "ftl_ckpt_last_error", [], ctypes.c_char_p)
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -301,3 +305,37 @@ def dp_finalize(slots, world, hyper, stats, loss_out, clip=True):
 def dp_adamw_allgather(peer_p, g, m, v, rank, world, lo, n, hyper, stats, status, max_ctas=0):
     _check(lib().ftl_dp_adamw_allgather(_ptr(peer_p), _ptr(g), _ptr(m), _ptr(v), rank, world, lo, n, _ptr(hyper),
                                         _ptr(stats), _ptr(status), max_ctas, _stream()), "ftl_dp_adamw_allgather")
+
+
+# ---- checkpoint snapshot engine (csrc/ckpt_io.cu) -----------------------------------------------------
+def ckpt_init(stage_bytes: int = 256 << 20) -> None:
+    code = lib().ftl_ckpt_init(stage_bytes)
+    if code != 0:
+        raise NativeError(f"ftl_ckpt_init failed: {lib().ftl_ckpt_last_error().decode()}")
+
+
+def _seg_arrays(segments):
+    n = len(segments)
+    ptrs = (c_void_p * n)(*[c_void_p(p) for p, _, _ in segments])
+    sizes = (c_int64 * n)(*[s for _, s, _ in segments])
+    offs = (c_int64 * n)(*[o for _, _, o in segments])
+    return n, ptrs, sizes, offs
+
+
+def ckpt_write(path: str, segments, nthreads: int = 4, fsync: bool = True) -> dict:
+    """segments: list of (device_ptr, nbytes, file_offset).  Blocks until the data is written (and fsynced)."""
+    n, ptrs, sizes, offs = _seg_arrays(segments)
+    t = (ctypes.c_double * 4)()
+    code = lib().ftl_ckpt_write(path.encode(), n, ptrs, sizes, offs, nthreads, int(fsync), t)
+    if code != 0:
+        raise NativeError(f"ftl_ckpt_write({path}) failed: {lib().ftl_ckpt_last_error().decode()}")
+    return {"d2h_s": t[0], "write_s": t[1], "fsync_s": t[2], "total_s": t[3]}
+
+
+def ckpt_read(path: str, segments, nthreads: int = 4) -> dict:
+    n, ptrs, sizes, offs = _seg_arrays(segments)
+    t = (ctypes.c_double * 4)()
+    code = lib().ftl_ckpt_read(path.encode(), n, ptrs, sizes, offs, nthreads, t)
+    if code != 0:
+        raise NativeError(f"ftl_ckpt_read({path}) failed: {lib().ftl_ckpt_last_error().decode()}")
+    return {"total_s": t[3]}

@@ -81,16 +81,8 @@ class DPNativeTrainer(NativeTrainer):
             dist.all_gather_into_tensor(buf, buf[self.lo:self.lo + self.shard].clone())
         torch.cuda.synchronize()
 
-    def save_fn(self):
-        from ..ckpt.layout import save_checkpoint
-
-        def save(checkpoint_path, jobid, model, optimizer, lr_scheduler, training_step, **kw):
-            self.sync_optimizer_state()
-            path = save_checkpoint(checkpoint_path, jobid, model, optimizer, lr_scheduler, training_step, **kw)
-            self.env.barrier()
-            return path
-
-        return save
+    def _moment_range(self):
+        return self.lo, self.lo + self.shard
 
     def load_state(self, ckpt: dict) -> None:
         super().load_state(ckpt)

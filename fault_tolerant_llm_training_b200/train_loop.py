@@ -86,7 +86,8 @@ def train(args) -> None:
                            warmup_steps=args.lr_warmup_steps, grad_max_norm=args.grad_max_norm,
                            clip_mode=args.clip_mode, seed=args.seed, parallel=args.parallel,
                            fused_optimizer=args.fused_optimizer, bucket_mb=args.bucket_mb,
-                           cuda_graph=args.cuda_graph)
+                           cuda_graph=args.cuda_graph, keep_shards=args.sharded_checkpoint,
+                           consolidate=not args.no_consolidate)
     if checkpoint is not None:
         trainer.load_state(checkpoint)
         logger.info("Model loaded from checkpoint")
@@ -116,12 +117,7 @@ def train(args) -> None:
                 if not (args.checkpoint_id and training_step == first_step):
                     raise Exception("Simulated exception to test signal handler", -1)
             if args.checkpoint_every and training_step > first_step and training_step % args.checkpoint_every == 0:
-                from .ckpt.layout import save_checkpoint
-                from .config import job_id
-                (trainer.save_fn() or save_checkpoint)(
-                    args.checkpoint_path, job_id(), trainer.model, trainer.optimizer, trainer.lr_scheduler,
-                    training_step, data_state=_data_state(stream, env), rank=env.rank,
-                    world_size=env.world_size, logger=logger)
+                _save_now(trainer, args, training_step, stream, env)
                 logger.info(f"Periodic checkpoint saved at step {training_step}")
 
             input_ids, labels = next(stream)
@@ -141,12 +137,7 @@ def train(args) -> None:
             training_step += 1
         logger.info("Training completed")
         if args.save_final:
-            from .ckpt.layout import save_checkpoint
-            from .config import job_id
-            (trainer.save_fn() or save_checkpoint)(
-                args.checkpoint_path, job_id(), trainer.model, trainer.optimizer, trainer.lr_scheduler,
-                training_step, data_state=_data_state(stream, env), rank=env.rank,
-                world_size=env.world_size, logger=logger)
+            _save_now(trainer, args, training_step, stream, env)
             logger.info(f"Final checkpoint saved at step {training_step}")
     except Exception as e:  # noqa: BLE001 — every interruption goes through the same handler (train.py:121-129)
         error_type = error_type_of(e)
@@ -155,7 +146,7 @@ def train(args) -> None:
         handle_exit(trainer.model, trainer.optimizer, trainer.lr_scheduler, training_step,
                     args.checkpoint_path, error_type, logger,
                     data_state=_data_state(stream, env) if error_type in (-1, 10) else None,
-                    save_fn=trainer.save_fn(),
+                    save_fn=trainer.save_fn(), finalize_fn=trainer.finalize_fn(),
                     made_progress=training_step > first_step, **exit_kw)
     finally:
         stream.close()
@@ -163,6 +154,21 @@ def train(args) -> None:
         flags.uninstall()
         env.shutdown()
     sys.exit(0)  # exit code 0 on every path, as the reference (train.py:119, 129)
+
+
+def _save_now(trainer, args, training_step, stream, env) -> None:
+    """Checkpoint outside the exit handler (periodic / final): same writers, same layout."""
+    from .ckpt.layout import save_checkpoint
+    from .config import job_id
+
+    if hasattr(trainer, "drain"):
+        trainer.drain()
+    (trainer.save_fn() or save_checkpoint)(
+        args.checkpoint_path, job_id(), trainer.model, trainer.optimizer, trainer.lr_scheduler, training_step,
+        data_state=_data_state(stream, env), rank=env.rank, world_size=env.world_size, logger=logger)
+    fin = trainer.finalize_fn()
+    if fin is not None:
+        fin(logger=logger)
 
 
 def _data_state(stream: BatchStream, env):

@@ -76,12 +76,18 @@ class TorchTrainer:
 
     # ---- checkpoint plumbing ----
     def load_state(self, ckpt: dict) -> None:
+        if "_sharded_dir" in ckpt:  # shards written by the B200 engine, resumed on the portable path
+            from .ckpt.sharded import assemble_payload
+            ckpt = assemble_payload(ckpt["_sharded_dir"], ckpt["_manifest"])
         self.model.load_state_dict(ckpt["model"], strict=True)  # strict
         self.optimizer.load_state_dict(ckpt["optimizer"])
         self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
 
     def save_fn(self):
         return None  # default single-writer save (ckpt.layout.save_checkpoint)
+
+    def finalize_fn(self):
+        return None
 
     def loss_value(self, loss: torch.Tensor) -> float:
         return float(loss.item())
@@ -93,7 +99,7 @@ class TorchTrainer:
 def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
                  grad_max_norm: float = 1.0, clip_mode: str = "clip", seed: int = 0, parallel: str = "auto",
                  fused_optimizer: bool = False, bucket_mb: int = 512, cuda_graph: bool = False,
-                 force_torch: bool = False):
+                 force_torch: bool = False, keep_shards: bool = False, consolidate: bool = True):
     """Factory used by train.py, bench.py and the tests."""
     if parallel == "auto":
         parallel = "dp" if env.distributed else "none"
@@ -107,6 +113,7 @@ def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: floa
 
         return NativeTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps,
                              grad_max_norm=grad_max_norm, clip_mode=clip_mode, seed=seed,
-                             parallel=parallel, bucket_mb=bucket_mb, cuda_graph=cuda_graph)
+                             parallel=parallel, bucket_mb=bucket_mb, cuda_graph=cuda_graph,
+                             keep_shards=keep_shards, consolidate=consolidate)
     return TorchTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps, grad_max_norm=grad_max_norm,
                         clip_mode=clip_mode, seed=seed, fused_optimizer=fused_optimizer)

@@ -69,3 +69,40 @@ def test_trainer_steps_reduce_loss_and_checkpoint_roundtrip(tmp_path):
     # the torch-AdamW layout loads into a stock torch optimizer too (what the reference does on resume)
     opt = torch.optim.AdamW(build_model(CFG, torch.bfloat16, "cpu").parameters(), lr=1e-3)
     opt.load_state_dict(ck["optimizer"])
+
+
+def test_sharded_checkpoint_roundtrip_and_reference_layout(tmp_path):
+    """Native snapshot engine: shards -> manifest (durable) -> consolidated reference-layout file; resume from
+    either gives a bitwise-identical continuation."""
+    import os
+    from fault_tolerant_llm_training_b200.ckpt.layout import load_checkpoint
+    from fault_tolerant_llm_training_b200.ckpt.sharded import MANIFEST, shard_dir
+    tr = _trainer(keep_shards=True)
+    inputs, labels = _batch(2)
+    for _ in range(4):
+        tr.step(inputs, labels)
+    tr.drain()
+    d = tr.save_fn()(str(tmp_path), "55", tr.model, tr.optimizer, tr.lr_scheduler, 4, data_state={"batches_consumed": 4})
+    assert os.path.exists(os.path.join(d, MANIFEST)) and d == shard_dir(str(tmp_path), "55")
+    assert tr.checkpointer.timings["bytes_this_rank"] == 3 * 2 * tr.flat.numel
+    # (a) resume straight from the shard directory (as after a kill during consolidation)
+    ck_sh = load_checkpoint(str(tmp_path), "55")
+    assert "_sharded_dir" in ck_sh and ck_sh["training_step"] == 4
+    tr_a = _trainer(seed=77)
+    tr_a.load_state(ck_sh)
+    # (b) consolidate, then resume from the reference-layout file
+    out = tr.finalize_fn()()
+    assert out and os.path.exists(out)
+    ck = load_checkpoint(str(tmp_path), "55")
+    assert list(ck.keys())[:4] == ["model", "optimizer", "lr_scheduler", "training_step"]
+    assert ck["data_state"] == {"batches_consumed": 4} and len(ck["model"]) == 3 + 9 * CFG.n_layers
+    tr_b = _trainer(seed=78)
+    tr_b.load_state(ck)
+    want = tr.step(inputs, labels).item()
+    assert tr_a.step(inputs, labels).item() == want and tr_b.step(inputs, labels).item() == want
+    for p, q, r in zip(tr.model.parameters(), tr_a.model.parameters(), tr_b.model.parameters()):
+        assert torch.equal(p, q) and torch.equal(p, r)
+    assert tr_a.optimizer.steps_done == tr_b.optimizer.steps_done == 5
+    # stock torch AdamW accepts the consolidated optimizer state (reference resume path, train.py:70-72)
+    opt = torch.optim.AdamW(build_model(CFG, torch.bfloat16, "cpu").parameters(), lr=1e-3)
+    opt.load_state_dict(ck["optimizer"])
