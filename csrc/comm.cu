@@ -89,7 +89,7 @@ dp_reduce_scatter_kernel(__nv_bfloat16* const* __restrict__ peer_g, int rank, in
                 for (int j = 0; j < 8; ++j) s[j] += f[j];
             }
             const bf16x8 o = pack8(s);
-            st8(dst + i * 8, o);
+            if (W > 1) st8(dst + i * 8, o);   // a single rank already holds the sum
             float f[8];
             unpack8(o, f);
 #pragma unroll
@@ -136,8 +136,9 @@ __global__ void __launch_bounds__(512)
 dp_adamw_allgather_kernel(__nv_bfloat16* const* __restrict__ peer_p, const __nv_bfloat16* __restrict__ g,
                           __nv_bfloat16* __restrict__ m, __nv_bfloat16* __restrict__ v, int rank, int64_t lo_vec,
                           int64_t nvec, const float* __restrict__ hyper, const float* __restrict__ stats,
-                          const uint32_t* __restrict__ status) {
+                          const uint32_t* __restrict__ status, unsigned long long* __restrict__ commits) {
     if (*status != 0 || stats[2] == 0.f) return;   // aborted step or non-finite norm: leave every copy untouched
+    if (commits && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(commits, 1ull);   // this range's update is applied
     const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4];
     const float bc1 = hyper[5], bc2_sqrt = hyper[6], coef = stats[1];
     const float step_size = lr / bc1, decay = 1.f - lr * wd;
@@ -244,14 +245,14 @@ FTL_API int ftl_dp_finalize(const float* slots, int world, const float* hyper, f
 }
 
 FTL_API int ftl_dp_adamw_allgather(void* const* peer_p, const void* g, void* m, void* v, int rank, int world, int64_t lo,
-                                   int64_t n, const float* hyper, const float* stats, const void* status, int max_ctas,
-                                   cudaStream_t stream) {
+                                   int64_t n, const float* hyper, const float* stats, const void* status, void* commits,
+                                   int max_ctas, cudaStream_t stream) {
     if (lo % 8 || n % 8 || n <= 0) return (int)cudaErrorInvalidValue;
     const int grid = comm_grid(n / 8, max_ctas);
     auto P = (__nv_bfloat16* const*)peer_p;
     auto S = (const uint32_t*)status;
 #define AG_CASE(W) case W: dp_adamw_allgather_kernel<W><<<grid, 512, 0, stream>>>(P, (const __nv_bfloat16*)g, \
-        (__nv_bfloat16*)m, (__nv_bfloat16*)v, rank, lo / 8, n / 8, hyper, stats, S); break;
+        (__nv_bfloat16*)m, (__nv_bfloat16*)v, rank, lo / 8, n / 8, hyper, stats, S, (unsigned long long*)commits); break;
     switch (world) { AG_CASE(1) AG_CASE(2) AG_CASE(3) AG_CASE(4) AG_CASE(5) AG_CASE(6) AG_CASE(7) AG_CASE(8)
         default: return (int)cudaErrorInvalidValue; }
 #undef AG_CASE

@@ -70,14 +70,12 @@ class FlatCheckpointer:
 
     # -- which flat ranges this rank writes ---------------------------------------------------------------
     def owned_ranges(self) -> List[Tuple[str, int, int]]:
-        t = self.t
-        W, r, n = t.env.world_size, t.env.rank, t.flat.numel
-        if W == 1:
-            return [("p", 0, n), ("m", 0, n), ("v", 0, n)]
-        shard = n // W
-        lo = r * shard
-        # parameters are replicated: each rank writes 1/W of them so the file system sees W parallel writers
-        return [("p", lo, lo + shard), ("m", lo, lo + shard), ("v", lo, lo + shard)]
+        # moments: exactly the ranges this rank maintains.  Parameters are replicated; each rank writes the same
+        # ranges of them, so the file system sees W parallel writers of 1/W each.
+        out = []
+        for lo, hi in self.t._moment_ranges():
+            out += [("p", lo, hi), ("m", lo, hi), ("v", lo, hi)]
+        return out
 
     # -- save ---------------------------------------------------------------------------------------------------
     def save(self, checkpoint_path: str, jobid: str, model, optimizer, lr_scheduler, training_step: int, *,

@@ -149,11 +149,14 @@ class BatchStream:
         self._q: Optional[queue.Queue] = None
         self._thread: Optional[threading.Thread] = None
         self._stop = threading.Event()
-        self._produced_from = 0
+        self._history = {}   # packed mode: dataset state before batch i, for the last few batches (rewind)
 
     # -- production ---------------------------------------------------------
     def _make(self, batch_index: int) -> Tuple[torch.Tensor, torch.Tensor]:
         if self.packed:
+            self._history[batch_index] = self.dataset.state_dict()
+            for k in [k for k in self._history if k < batch_index - 8]:
+                del self._history[k]
             pairs = [next(self.dataset) for _ in range(self.batch_size)]
             inputs = torch.stack([p[0] for p in pairs])
             labels = torch.stack([p[1] for p in pairs])
@@ -199,7 +202,7 @@ class BatchStream:
 
     def __next__(self) -> Tuple[torch.Tensor, torch.Tensor]:
         if self._prefetch <= 0:
-            batch = self._make(self.batches_consumed)
+            batch = self._make(self.batches_consumed)  # packed mode: index only labels the history entry
         else:
             if self._thread is None:
                 self._start()
@@ -224,6 +227,18 @@ class BatchStream:
         self.batches_consumed = int(state["batches_consumed"])
         if self.packed and "dataset" in state:
             self.dataset.load_state_dict(state["dataset"])
+
+    def rewind(self, batches_consumed: int) -> None:
+        """Move the position back to just before batch `batches_consumed` (a step that was fetched but whose
+        update never committed).  Padded mode is O(1); packed mode restores the recorded dataset state."""
+        if batches_consumed == self.batches_consumed:
+            return
+        self.close()
+        if self.packed:
+            if batches_consumed not in self._history:
+                raise ValueError(f"no recorded dataset state for batch {batches_consumed}")
+            self.dataset.load_state_dict(self._history[batches_consumed])
+        self.batches_consumed = batches_consumed
 
     def fast_forward(self, batches: int) -> None:
         """Position restore for checkpoints that carry no dataset state (files

@@ -213,6 +213,17 @@ class NativeEngine:
                 for k in ("o", "w1", "w2", "w3", "an", "fn"):
                     lw[tag + k] = fv(buf, names[k])
             self.lw.append(lw)
+        # Pipelining hooks (parallel/pipeline.py).  Buckets: 0 = embedding, 1+i = layer i, L+1 = final norm + head.
+        #   hook_params(b): called before the first kernel that reads bucket b's parameters
+        #   hook_grads(b):  called after the last kernel that writes bucket b's gradients
+        self.hook_params = None
+        self.hook_grads = None
+
+    def _need(self, upto: int) -> None:
+        if self.hook_params is not None:
+            while self._params_waited < upto:
+                self._params_waited += 1
+                self.hook_params(self._params_waited)
 
     # ---- GEMM dispatch: C = A @ B^T (nt), A @ B (nn), A^T @ B (tn) -------------------------------
     @staticmethod
@@ -260,8 +271,11 @@ class NativeEngine:
         c, T = self.cfg, self.T
         H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
         rot = (H + KV) * hd
+        self._params_waited = -1
+        self._need(0)
         N.embedding_fwd(tokens.view(-1), self.w_emb, self.x[0])
         for i, lw in enumerate(self.lw):
+            self._need(i + 2)   # this layer, and the norm weight of the next one (or the head) used by the fused norm
             if i == 0:
                 N.rmsnorm_fwd(self.x[0], lw["wan"], c.norm_eps, self.xn[0], self.rstd1[0])
             self.gemm_nt(self.xn[i], lw["wqkv"], self.qkv[i])
@@ -298,6 +312,8 @@ class NativeEngine:
         self.gemm_nn(dl, self.w_out, self.dtmp)                   # d xf
         dx, spare = self.dx_a, self.dx_b
         N.rmsnorm_bwd(self.dtmp, self.x[L], self.w_fn, self.rstd_f, dx, self.g_fn, self.norm_scratch)
+        if self.hook_grads is not None:
+            self.hook_grads(L + 1)
         for i in range(L - 1, -1, -1):
             lw = self.lw[i]
             # x_{i+1} = h + w2(act)
@@ -322,10 +338,14 @@ class NativeEngine:
             N.rmsnorm_bwd(self.dtmp, self.x[i], lw["wan"], self.rstd1[i], spare, lw["gan"], self.norm_scratch,
                           dres=self.dh)
             dx, spare = spare, dx
+            if self.hook_grads is not None:
+                self.hook_grads(i + 1)
         # embedding: deterministic scatter-add
         self.g_emb.zero_()
         sorted_tok, perm = torch.sort(tokens.view(-1), stable=True)
         N.embedding_bwd(sorted_tok, perm, dx, self.g_emb)
+        if self.hook_grads is not None:
+            self.hook_grads(0)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -414,20 +434,27 @@ class NativeTrainer:
         st["flt_h"][:len(flt)] = torch.tensor(flt, dtype=torch.float32)
         st["dev"].copy_(st["host"], non_blocking=True)                  # the one H2D copy of the step
         inv_n, hyper = st["flt_d"][0:1], st["flt_d"][1:9]
+        self._begin_step(hyper)
         loss = self.engine.forward(st["tok_d"], st["lab_d"], inv_n)
         self.engine.backward(st["tok_d"])
         self._reduce_and_update(hyper, loss)
         self.lr_scheduler.step()
-        # result: loss, grad norm, clip coef, finite, comm status
-        self.result_dev[0:1].copy_(loss)
-        self.result_dev[1:4].copy_(self.stats[0:3])
-        self._write_status(self.result_dev[4:5])
-        self.result_host[slot].copy_(self.result_dev, non_blocking=True)  # the one D2H copy of the step
-        self.events[slot].record()
-        handle = LossHandle(self.result_host[slot], self.events[slot])
+        handle = self._publish_result(loss, slot)
         self._pending.append(handle)
         self.kernel_launches_per_step = N.LAUNCHES - launches0
         return handle
+
+    def _begin_step(self, hyper: torch.Tensor) -> None:
+        pass
+
+    def _publish_result(self, loss: torch.Tensor, slot: int) -> "LossHandle":
+        """One D2H copy per step: loss, grad norm, clip coefficient, finite flag, comm status."""
+        self.result_dev[0:1].copy_(loss)
+        self.result_dev[1:4].copy_(self.stats[0:3])
+        self._write_status(self.result_dev[4:5])
+        self.result_host[slot].copy_(self.result_dev, non_blocking=True)
+        self.events[slot].record()
+        return LossHandle(self.result_host[slot], self.events[slot])
 
     def _inspect(self, old: "LossHandle") -> None:
         """Host-side check of a finished step (two steps late, see step())."""
@@ -463,9 +490,9 @@ class NativeTrainer:
         self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
         torch.cuda.synchronize()
 
-    def _moment_range(self):
-        """Flat range of exp_avg / exp_avg_sq this rank maintains."""
-        return 0, self.flat.numel
+    def _moment_ranges(self):
+        """Flat ranges of exp_avg / exp_avg_sq this rank maintains."""
+        return [(0, self.flat.numel)]
 
     def _load_sharded(self, ckpt: dict) -> None:
         """Shard files -> device, straight through the native reader (no CPU state_dict is ever built)."""
@@ -476,11 +503,11 @@ class NativeTrainer:
         n_ck = m["flat_numel"]   # padding at the tail may differ with the world size; the payload does not
         n = min(n_ck, f.numel)
         read_range_to_device(d, m, "p", 0, n, f.p[:n])
-        lo, hi = self._moment_range()
-        hi = min(hi, n)
-        if lo < hi:
-            read_range_to_device(d, m, "m", lo, hi, f.m[lo:hi])
-            read_range_to_device(d, m, "v", lo, hi, f.v[lo:hi])
+        for lo, hi in self._moment_ranges():
+            hi = min(hi, n)
+            if lo < hi:
+                read_range_to_device(d, m, "m", lo, hi, f.m[lo:hi])
+                read_range_to_device(d, m, "v", lo, hi, f.v[lo:hi])
         g = m["optimizer"]["param_groups"][0]
         for k, v in g.items():
             self.optimizer.param_groups[0][k] = tuple(v) if k == "betas" else v

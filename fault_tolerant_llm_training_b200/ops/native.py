@@ -73,7 +73,7 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_dp_reduce_scatter", [P, I, I, I64, I64, P, P, I, P])
     _sig(L, "ftl_dp_publish", [P, I, P, P, I, I, P])
     _sig(L, "ftl_dp_finalize", [P, I, P, P, P, I, P])
-    _sig(L, "ftl_dp_adamw_allgather", [P, P, P, P, I, I, I64, I64, P, P, P, I, P])
+    _sig(L, "ftl_dp_adamw_allgather", [P, P, P, P, I, I, I64, I64, P, P, P, P, I, P])
     _sig(L, "ftl_ckpt_init", [I64])
     _sig(L, "ftl_ckpt_write", [ctypes.c_char_p, I, P, P, P, I, I, P])
     _sig(L, "ftl_ckpt_read", [ctypes.c_char_p, I, P, P, P, I, P])
@@ -302,9 +302,10 @@ def dp_finalize(slots, world, hyper, stats, loss_out, clip=True):
            "ftl_dp_finalize")
 
 
-def dp_adamw_allgather(peer_p, g, m, v, rank, world, lo, n, hyper, stats, status, max_ctas=0):
+def dp_adamw_allgather(peer_p, g, m, v, rank, world, lo, n, hyper, stats, status, commits=None, max_ctas=0):
     _check(lib().ftl_dp_adamw_allgather(_ptr(peer_p), _ptr(g), _ptr(m), _ptr(v), rank, world, lo, n, _ptr(hyper),
-                                        _ptr(stats), _ptr(status), max_ctas, _stream()), "ftl_dp_adamw_allgather")
+                                        _ptr(stats), _ptr(status), _ptr(commits), max_ctas, _stream()),
+           "ftl_dp_adamw_allgather")
 
 
 # ---- checkpoint snapshot engine (csrc/ckpt_io.cu) -----------------------------------------------------

@@ -22,3 +22,14 @@ def build_lr_scheduler(optimizer, warmup_steps: int) -> LambdaLR:
     """A LambdaLR over a functools.partial, so `state_dict()["lr_lambdas"] == [{}]`
     exactly like the reference's scheduler and either side can load the other's."""
     return LambdaLR(optimizer, functools.partial(warmup_constant_factor, warmup_steps))
+
+
+def rewind_lr_scheduler(scheduler: LambdaLR, epoch: int) -> None:
+    """Put a LambdaLR back to the state it had after `epoch` step() calls (used when steps that the host had
+    already counted turn out not to have been applied on the device)."""
+    scheduler.last_epoch = epoch
+    scheduler._step_count = epoch + 1
+    lrs = [base * lmbda(epoch) for base, lmbda in zip(scheduler.base_lrs, scheduler.lr_lambdas)]
+    for group, lr in zip(scheduler.optimizer.param_groups, lrs):
+        group["lr"] = lr
+    scheduler._last_lr = lrs

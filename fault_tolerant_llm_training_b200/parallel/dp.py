@@ -41,6 +41,7 @@ class DPNativeTrainer(NativeTrainer):
         self.comm_status = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.rs_partials = torch.zeros(N.dp_partials(), dtype=torch.float32, device=self.device)
         self.epoch = 0
+        self.commits = torch.zeros(1, dtype=torch.int64, device=self.device)
         self.barrier_timeout_ms = 120000
         bufs = {"p": lambda n: self.symm.tensor("p", torch.bfloat16), "g": lambda n: self.symm.tensor("g", torch.bfloat16)}
         flat = FlatState(self.model, self.device, buffers=bufs, pad_to=pad)
@@ -61,7 +62,7 @@ class DPNativeTrainer(NativeTrainer):
         self._barrier()
         N.dp_finalize(self.slots, W, hyper, self.stats, loss, clip=(self.clip_mode == "clip"))
         N.dp_adamw_allgather(self.symm.table("p"), f.g, f.m, f.v, env.rank, W, self.lo, self.shard, hyper, self.stats,
-                             self.comm_status)
+                             self.comm_status, self.commits)
         self._barrier()
         self.optimizer.steps_done += 1
         self.optimizer._opt_called = True   # the update ran inside the fused kernel, not through optimizer.step()
@@ -81,8 +82,8 @@ class DPNativeTrainer(NativeTrainer):
             dist.all_gather_into_tensor(buf, buf[self.lo:self.lo + self.shard].clone())
         torch.cuda.synchronize()
 
-    def _moment_range(self):
-        return self.lo, self.lo + self.shard
+    def _moment_ranges(self):
+        return [(self.lo, self.lo + self.shard)]
 
     def load_state(self, ckpt: dict) -> None:
         super().load_state(ckpt)

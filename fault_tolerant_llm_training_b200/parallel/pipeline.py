@@ -1,0 +1,169 @@
+"""Pipelined update engine for 1..8 GPUs: gradient reduce-scatter overlapped with backward, sharded
+AdamW + parameter all-gather overlapped with the next step's forward (BASELINE.json fused path 1).
+
+The flat parameter space is cut into buckets in forward order — embedding | layer 0 | ... | layer L-1 |
+final norm + LM head — and every bucket is split into W equal sub-shards; rank r owns sub-shard r of every
+bucket (so all ranks have reducible work as soon as ANY bucket's gradients exist).  A second CUDA stream
+runs the data plane of csrc/comm.cu:
+
+  backward of bucket b done (event) ──► [barrier] reduce-scatter ⊕ norm² of sub-shard (b, r)      phase 1
+  all buckets reduced ──► publish {sumsq, loss} ► [barrier] ► finalize (global norm, clip, loss) ► result D2H
+  for b in forward order: clip ⊕ AdamW ⊕ all-gather of sub-shard (b, r) ► [barrier] ► event "bucket b ready"
+                                                                                                   phase 2
+  next step's forward waits on "bucket b ready" just before the first kernel that reads bucket b.
+
+Phase 1 hides under the backward GEMMs, phase 2 under the next forward: the HBM-bound optimizer and the
+NVLink traffic run while the tensor cores are busy.  With W = 1 the same schedule (without barriers and
+peer traffic) overlaps the 113 GB AdamW pass and the gradient-norm pass with compute.  Barriers are only
+issued for W > 1.  Global-norm clipping needs the norm of ALL gradients before any update, which is why
+the update is a second phase rather than part of the reduce-scatter kernel.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Tuple
+
+import torch
+
+from ..models.engine import FlatState, LossHandle, NativeTrainer
+from ..ops import native as N
+from .symm import SymmetricBuffers
+
+
+class PipelinedTrainer(NativeTrainer):
+    RS_CTAS = int(os.environ.get("FTL_RS_CTAS", "32"))       # SMs' worth of CTAs lent to phase 1 while GEMMs run
+    UPD_CTAS = int(os.environ.get("FTL_UPD_CTAS", "64"))     # ... and to phase 2
+
+    # ---- state ---------------------------------------------------------------------------------------------------
+    def _make_flat_state(self) -> FlatState:
+        env, W = self.env, self.env.world_size
+        from ..models.llama import flat_size, param_layout
+        layout = param_layout(self.model)
+        numel = (flat_size(layout) + 1023) // 1024 * 1024
+        flag_words = N.lib().ftl_comm_flag_words()
+        self.symm = SymmetricBuffers(env, {"p": numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64})
+        bufs = {"p": lambda n: self.symm.tensor("p", torch.bfloat16), "g": lambda n: self.symm.tensor("g", torch.bfloat16)}
+        flat = FlatState(self.model, self.device, buffers=bufs, pad_to=1024)
+        assert flat.numel == numel
+        # buckets in forward order
+        L = self.cfg.n_layers
+        starts = [flat.index["tok_embeddings.weight"][0]]
+        starts += [flat.index[f"layers.{i}.attention.wq.weight"][0] for i in range(L)]
+        starts += [flat.index["norm.weight"][0], numel]
+        self.buckets: List[Tuple[int, int]] = [(starts[i], starts[i + 1]) for i in range(L + 2)]
+        self.sub: List[Tuple[int, int]] = []          # this rank's sub-shard of each bucket
+        for lo, hi in self.buckets:
+            sz = ((hi - lo + W - 1) // W + 7) // 8 * 8
+            a = min(lo + env.rank * sz, hi)
+            self.sub.append((a, min(a + sz, hi)))
+        NB = len(self.buckets)
+        self.parts = N.dp_partials(self.RS_CTAS)
+        self.rs_partials = torch.zeros(NB * self.parts, dtype=torch.float32, device=self.device)
+        self.comm_status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.commits = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.slots = self.symm.tensor("slots", torch.float32)
+        self.epoch = 0
+        self.barrier_timeout_ms = int(os.environ.get("FTL_BARRIER_TIMEOUT_MS", "120000"))
+        self.comm = torch.cuda.Stream(device=self.device)
+        self.ev_grad = [torch.cuda.Event() for _ in range(NB)]
+        self.ev_param = [torch.cuda.Event() for _ in range(NB)]
+        self.ev_step = torch.cuda.Event()
+        self._params_pending = False
+        self._hyper = None
+        return flat
+
+    def _moment_ranges(self):
+        return [(a, b) for a, b in self.sub if b > a]
+
+    # ---- hooks called from the engine ----------------------------------------------------------------------------
+    def _ensure_engine(self, B: int, S: int) -> None:
+        fresh = self.engine is None or (self.engine.B, self.engine.S) != (B, S)
+        super()._ensure_engine(B, S)
+        if fresh:
+            self.engine.hook_params = self._wait_params
+            self.engine.hook_grads = self._grads_done
+
+    def _wait_params(self, b: int) -> None:
+        """Forward is about to read bucket b: wait until last step's update of it has landed everywhere."""
+        if self._params_pending:
+            torch.cuda.current_stream().wait_event(self.ev_param[b])
+
+    def _barrier(self) -> None:
+        if self.env.world_size > 1:
+            self.epoch += 1
+            N.barrier(self.symm.table("flags"), self.env.rank, self.env.world_size, self.epoch, self.comm_status,
+                      self.barrier_timeout_ms)
+
+    def _grads_done(self, b: int) -> None:
+        """Backward finished writing bucket b's gradients: reduce this rank's sub-shard on the comm stream."""
+        self.ev_grad[b].record()
+        a, e = self.sub[b]
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(self.ev_grad[b])
+            self._barrier()          # every rank's bucket-b gradients are complete
+            part = self.rs_partials[b * self.parts:(b + 1) * self.parts]
+            if e > a:
+                N.dp_reduce_scatter(self.symm.table("g"), self.env.rank, self.env.world_size, a, e - a, part,
+                                    self.comm_status, max_ctas=self.RS_CTAS)
+            else:
+                part.zero_()
+
+    # ---- step pieces ---------------------------------------------------------------------------------------------
+    def _begin_step(self, hyper: torch.Tensor) -> None:
+        self._hyper = hyper
+        # the comm stream must not start this step's phase 1 before the staging copy (hyper) has been issued
+        self.ev_step.record()
+        self.comm.wait_event(self.ev_step)
+
+    def _reduce_and_update(self, hyper: torch.Tensor, loss: torch.Tensor) -> None:
+        env, f, W = self.env, self.flat, self.env.world_size
+        with torch.cuda.stream(self.comm):
+            N.dp_publish(self.rs_partials, self.rs_partials.numel(), loss, self.symm.table("slots"), env.rank, W)
+            self._barrier()          # all slots written; nobody still reads my gradients for phase 1
+            N.dp_finalize(self.slots, W, hyper, self.stats, loss, clip=(self.clip_mode == "clip"))
+            self._result_handle = self._publish_result_on_comm(loss)
+            for b, (a, e) in enumerate(self.sub):
+                if e > a:
+                    N.dp_adamw_allgather(self.symm.table("p"), f.g, f.m, f.v, env.rank, W, a, e - a, hyper, self.stats,
+                                         self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
+                self._barrier()      # bucket b is updated on every rank
+                self.ev_param[b].record()
+        self._params_pending = True
+        self.optimizer.steps_done += 1
+        self.optimizer._opt_called = True   # the update ran inside the fused kernels
+
+    def _publish_result_on_comm(self, loss: torch.Tensor) -> LossHandle:
+        slot = self._result_slot
+        self.result_dev[0:1].copy_(loss)
+        self.result_dev[1:4].copy_(self.stats[0:3])
+        self.result_dev[4:5].copy_(self.comm_status.to(torch.float32))
+        self.result_host[slot].copy_(self.result_dev, non_blocking=True)
+        self.events[slot].record()
+        return LossHandle(self.result_host[slot], self.events[slot])
+
+    def _publish_result(self, loss: torch.Tensor, slot: int) -> LossHandle:
+        return self._result_handle      # recorded on the comm stream right after finalize
+
+    def step(self, inputs, labels):
+        self._result_slot = self._slot   # ring slot this step will use (base class advances _slot)
+        return super().step(inputs, labels)
+
+    # ---- fault tolerance -----------------------------------------------------------------------------------------
+    def committed_updates(self) -> int:
+        """Number of optimizer steps fully applied on the device (each applies one update per non-empty bucket)."""
+        torch.cuda.synchronize()
+        per_step = sum(1 for a, e in self.sub if e > a)
+        return int(self.commits.item()) // max(per_step, 1)
+
+    def abort_peers(self) -> None:
+        if self.env.world_size > 1:
+            N.raise_abort(self.symm.table("flags"), self.env.world_size)
+            torch.cuda.synchronize()
+
+    def load_state(self, ckpt: dict) -> None:
+        super().load_state(ckpt)
+        torch.cuda.synchronize()
+        self.env.barrier()
+
+    def close(self) -> None:
+        torch.cuda.synchronize()

@@ -100,6 +100,8 @@ def train(args) -> None:
         logger.info("Starting training!")
     del checkpoint
     first_step = training_step
+    steps_base = getattr(trainer.optimizer, "steps_done", 0)
+    batches_base = stream.batches_consumed
 
     tokens_per_step = args.batch_size * args.sequence_length * env.world_size
     t_window, window_steps = time.perf_counter(), 0
@@ -143,6 +145,7 @@ def train(args) -> None:
         error_type = error_type_of(e)
         if error_type == -1 and not (len(e.args) >= 2 and e.args[1] == -1):
             logger.exception("Exception in the training loop")
+        training_step = _settle(trainer, stream, e, training_step, first_step, steps_base, batches_base, env)
         handle_exit(trainer.model, trainer.optimizer, trainer.lr_scheduler, training_step,
                     args.checkpoint_path, error_type, logger,
                     data_state=_data_state(stream, env) if error_type in (-1, 10) else None,
@@ -154,6 +157,31 @@ def train(args) -> None:
         flags.uninstall()
         env.shutdown()
     sys.exit(0)  # exit code 0 on every path, as the reference (train.py:119, 129)
+
+
+def _settle(trainer, stream, exc, training_step, first_step, steps_base, batches_base, env) -> int:
+    """Bring the host-side counters in line with what the device actually applied before a checkpoint is taken.
+
+    The host enqueues steps ahead of the GPU.  A step whose gradient norm was non-finite, or that was cut short
+    by a failing peer (abort word / barrier timeout), leaves parameters and moments untouched on the device,
+    but the host already counted it.  The update kernels count what they applied; everything else is rewound to
+    that count, so "saved at step N" again means exactly N updates."""
+    from .ft.signals import PeerAbort, TrainingInterrupt
+    from .optim.lr import rewind_lr_scheduler
+
+    if not hasattr(trainer, "committed_updates"):
+        return training_step
+    if env.distributed and not isinstance(exc, (TrainingInterrupt, PeerAbort)):
+        trainer.abort_peers()   # peers parked in a device barrier fall through instead of waiting for this rank
+    done = first_step + trainer.committed_updates()
+    done = env.max_int(-env.max_int(-done)) if env.distributed else done   # min over ranks (they agree; belt and braces)
+    if done != training_step or trainer.optimizer.steps_done != steps_base + (done - first_step):
+        logger.info(f"[EXIT HANDLER] device applied {done - first_step} updates in this job; host had counted "
+                    f"{training_step - first_step}: rewinding to step {done}")
+        trainer.optimizer.steps_done = steps_base + (done - first_step)
+        rewind_lr_scheduler(trainer.lr_scheduler, done)
+    stream.rewind(batches_base + (done - first_step))   # a batch fetched for a step that never committed is re-served
+    return done
 
 
 def _save_now(trainer, args, training_step, stream, env) -> None:

@@ -108,8 +108,12 @@ def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: floa
 
         if env.distributed and parallel == "none":
             raise ValueError("--parallel none with WORLD_SIZE > 1: ranks would train unsynchronised copies")
-        if env.distributed:
-            from .parallel.dp import DPNativeTrainer as NativeTrainer  # noqa: F811 (dp; fsdp shares the engine)
+        import os
+        if os.environ.get("FTL_PIPELINE", "1") != "0":
+            # default: bucketed, overlapped reduce-scatter / AdamW / all-gather on a second stream (1..8 GPUs)
+            from .parallel.pipeline import PipelinedTrainer as NativeTrainer  # noqa: F811
+        elif env.distributed:
+            from .parallel.dp import DPNativeTrainer as NativeTrainer  # noqa: F811 (unpipelined reference schedule)
 
         return NativeTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps,
                              grad_max_norm=grad_max_norm, clip_mode=clip_mode, seed=seed,

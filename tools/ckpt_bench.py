@@ -37,12 +37,16 @@ def main():
     durable = time.perf_counter() - t0
     res = {"world": env.world_size, "signal_to_durable_s": round(env.max_float(durable), 3),
            "per_rank": {k: round(v, 3) for k, v in tr.checkpointer.timings.items()}}
-    if consolidate:
+    if env.is_main:
+        print(json.dumps(res), flush=True)
+    if consolidate and env.is_main:
+        # the box has room for one 48 GB copy on disk, so the consolidated file goes to tmpfs here
+        from fault_tolerant_llm_training_b200.ckpt.sharded import consolidate as do_consolidate, shard_dir as sd
         t1 = time.perf_counter()
-        tr.finalize_fn()()
+        out = do_consolidate(sd(out_dir, "bench"), "/dev/shm/ftl_checkpoint_bench.ckpt")
         res["consolidate_s"] = round(time.perf_counter() - t1, 3)
-        if env.is_main:
-            res["consolidated_bytes"] = os.path.getsize(os.path.join(out_dir, "checkpoint_bench.ckpt"))
+        res["consolidated_bytes"] = os.path.getsize(out)
+        os.remove(out)
     # resume from the shards: disk -> device through the native reader
     env.barrier()
     t2 = time.perf_counter()
