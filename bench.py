@@ -77,7 +77,8 @@ def _dist_max(value: float, device) -> float:
     import torch.distributed as dist
 
     if dist.is_initialized() and dist.get_world_size() > 1:
-        t = torch.tensor([value], dtype=torch.float64, device=device)
+        on_gpu = dist.get_backend() == "nccl"
+        t = torch.tensor([value], dtype=torch.float64, device=device if on_gpu else "cpu")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
     return value

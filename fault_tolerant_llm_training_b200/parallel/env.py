@@ -112,9 +112,12 @@ def init_dist(device_arg: str = "auto", timeout_s: int = 600) -> DistEnv:
         os.environ.setdefault("MASTER_PORT", "29511")
         td = datetime.timedelta(seconds=timeout_s)
         if not dist.is_initialized():
-            backend = "nccl" if device.type == "cuda" else "gloo"
-            kw = {"device_id": device} if device.type == "cuda" else {}
-            dist.init_process_group(backend=backend, rank=rank, world_size=world, timeout=td, **kw)
+            # The data plane is this framework's own NVLink kernels (csrc/comm.cu); torch.distributed is only the
+            # control plane (handle exchange, per-step scalars), so gloo suffices.  FTL_NCCL=1 brings NCCL up as
+            # the default group as well (needed only by the unpipelined DP schedule's moment all-gather).
+            use_nccl = device.type == "cuda" and os.environ.get("FTL_NCCL", "0") == "1"
+            kw = {"device_id": device} if use_nccl else {}
+            dist.init_process_group(backend="nccl" if use_nccl else "gloo", rank=rank, world_size=world, timeout=td, **kw)
             env.owns_pg = True
         env.ctrl = dist.new_group(backend="gloo", timeout=td)
     return env

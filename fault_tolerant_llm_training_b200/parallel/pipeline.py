@@ -31,8 +31,8 @@ from .symm import SymmetricBuffers
 
 
 class PipelinedTrainer(NativeTrainer):
-    RS_CTAS = int(os.environ.get("FTL_RS_CTAS", "32"))       # SMs' worth of CTAs lent to phase 1 while GEMMs run
-    UPD_CTAS = int(os.environ.get("FTL_UPD_CTAS", "64"))     # ... and to phase 2
+    RS_CTAS = int(os.environ.get("FTL_RS_CTAS", "96"))       # SMs' worth of CTAs lent to phase 1 while GEMMs run
+    UPD_CTAS = int(os.environ.get("FTL_UPD_CTAS", "0"))      # ... and to phase 2 (0 = 4 CTAs per SM: HBM-bound)
 
     # ---- state ---------------------------------------------------------------------------------------------------
     def _make_flat_state(self) -> FlatState:
@@ -64,7 +64,8 @@ class PipelinedTrainer(NativeTrainer):
         self.slots = self.symm.tensor("slots", torch.float32)
         self.epoch = 0
         self.barrier_timeout_ms = int(os.environ.get("FTL_BARRIER_TIMEOUT_MS", "120000"))
-        self.comm = torch.cuda.Stream(device=self.device)
+        # high priority: when an SM frees resources, the (small, memory-bound) data-plane CTAs are placed first
+        self.comm = torch.cuda.Stream(device=self.device, priority=-1)
         self.ev_grad = [torch.cuda.Event() for _ in range(NB)]
         self.ev_param = [torch.cuda.Event() for _ in range(NB)]
         self.ev_step = torch.cuda.Event()

@@ -59,10 +59,13 @@ def main():
         print(json.dumps(out), flush=True)
     # checkpoint path: gather moments, save on rank 0, reload everywhere
     save = tr.save_fn()
-    path = save("/tmp/ftl_dp_check", "dp", tr.model, tr.optimizer, tr.lr_scheduler, STEPS, rank=env.rank, world_size=W)
+    save("/tmp/ftl_dp_check", "dp", tr.model, tr.optimizer, tr.lr_scheduler, STEPS, rank=env.rank, world_size=W)
+    path = tr.finalize_fn()()       # rank 0 consolidates the W shard files into the reference layout
     env.barrier()
     if env.rank == 0:
         ck = torch.load(path, weights_only=False)
+        ref_sd = {k: v.float() for k, v in tr.model.state_dict().items()}
+        assert all(torch.equal(ck["model"][k].float(), ref_sd[k].cpu()) for k in ref_sd)
         nz = sum(int(s["exp_avg"].abs().sum() > 0) for s in ck["optimizer"]["state"].values())
         print(json.dumps({"ckpt_tensors_with_moments": nz, "of": len(ck["optimizer"]["state"])}), flush=True)
     env.shutdown()
