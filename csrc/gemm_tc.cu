@@ -27,6 +27,8 @@
 #include <cuda_bf16.h>
 #include <cudaTypedefs.h>
 
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "common/ptx.cuh"
@@ -53,7 +55,82 @@ struct GemmArgs {
     int seq_len, head_dim, rot_cols;
 };
 
-template <int kEpi, bool kAMn, bool kBMn>
+// One thread = one output row of the tile: TMEM (32 fp32 columns at a time) -> registers -> fused math -> 16-byte
+// global stores.  taddr addresses this warp's TMEM lane quarter of the accumulator stage.
+__device__ __forceinline__ void st16(__nv_bfloat16* p, const bf16x8& v) {
+    const int4& r = *reinterpret_cast<const int4*>(&v);
+    asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w) : "memory");
+}
+
+template <int kEpi>
+__device__ __forceinline__ void epilogue_tile(const GemmArgs& g, uint32_t taddr, int row, int n_blk) {
+                if (kEpi == EPI_SWIGLU) {
+                    const int h0 = n_blk * (BN / 2);   // first hidden column of this tile
+                    const int hidden = g.N / 2;
+    #pragma unroll 1
+                    for (int c = 0; c < BN / 2; c += 32) {
+                        uint32_t rg[32], ru[32];
+                        ptx::tmem_ld32(taddr + c, rg);
+                        ptx::tmem_ld32(taddr + BN / 2 + c, ru);
+                        ptx::tmem_ld_wait();
+                        if (row < g.M) {
+    #pragma unroll
+                            for (int v = 0; v < 4; ++v) {
+                                const int col = h0 + c + v * 8;
+                                if (col < hidden) {
+                                    float gt[8], up[8], act[8];
+    #pragma unroll
+                                    for (int j = 0; j < 8; ++j) {
+                                        gt[j] = round_bf16(__uint_as_float(rg[v * 8 + j]));
+                                        up[j] = round_bf16(__uint_as_float(ru[v * 8 + j]));
+                                        act[j] = round_bf16(gt[j] / (1.f + __expf(-gt[j]))) * up[j];
+                                    }
+                                    const int64_t off = (int64_t)row * g.ldc + col;
+                                    st16(g.C + off, pack8(act));
+                                    if (g.C_gate) st16(g.C_gate + off, pack8(gt));
+                                    if (g.C_up) st16(g.C_up + off, pack8(up));
+                                }
+                            }
+                        }
+                    }
+                } else {
+                    const int n0 = n_blk * BN;
+    #pragma unroll 1
+                    for (int c = 0; c < BN; c += 32) {
+                        uint32_t r[32];
+                        ptx::tmem_ld32(taddr + c, r);
+                        ptx::tmem_ld_wait();
+                        if (row < g.M) {
+    #pragma unroll
+                            for (int v = 0; v < 4; ++v) {
+                                const int col = n0 + c + v * 8;
+                                if (col < g.N) {
+                                    float f[8];
+    #pragma unroll
+                                    for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
+                                    if (kEpi == EPI_ROPE && col < g.rot_cols) {
+                                        const int pos = row % g.seq_len;
+                                        const int pair0 = (col % g.head_dim) >> 1;
+                                        const int64_t to = (int64_t)pos * (g.head_dim >> 1) + pair0;
+                                        const float4 cs = *reinterpret_cast<const float4*>(g.cos_t + to);
+                                        const float4 sn = *reinterpret_cast<const float4*>(g.sin_t + to);
+                                        const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
+    #pragma unroll
+                                        for (int j = 0; j < 4; ++j) {
+                                            const float a = round_bf16(f[2 * j]), b = round_bf16(f[2 * j + 1]);
+                                            f[2 * j] = a * cc[j] - b * ss[j];
+                                            f[2 * j + 1] = a * ss[j] + b * cc[j];
+                                        }
+                                    }
+                                    st16(g.C + (int64_t)row * g.ldc + col, pack8(f));
+                                }
+                            }
+                        }
+                    }
+                }
+}
+
+template <int kEpi, bool kAMn, bool kBMn, int kCluster>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
@@ -70,15 +147,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m_tiles = (g.M + BM - 1) / BM;
     const int n_tiles = (g.N + BN - 1) / BN;
-    const int num_tiles = m_tiles * n_tiles;
     const int num_kb = (g.K + BK - 1) / BK;
+    // A cluster of kCluster CTAs works on kCluster vertically adjacent tiles (same n block): they need the same
+    // B tile, so each CTA fetches 1/kCluster of it and TMA-multicasts that part into every CTA of the cluster.
+    // L2 -> SM traffic per CTA and k-block drops from 48 KB to 16 + 32/kCluster KB; at 48 KB the kernel is
+    // bound by L2 bandwidth (profiles/gemm_tc_v1_ncu.md), not by the tensor pipe.
+    const int crank = kCluster > 1 ? (int)ptx::cluster_ctarank() : 0;
+    const int cluster_id = blockIdx.x / kCluster, num_clusters = gridDim.x / kCluster;
+    const int m_groups = (m_tiles + kCluster - 1) / kCluster;
+    const int num_units = m_groups * n_tiles;
+    constexpr uint16_t kMask = (uint16_t)((1u << kCluster) - 1);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
         ptx::prefetch_tmap(&tmB);
         for (int i = 0; i < kStages; ++i) {
             ptx::mbar_init(&full[i], 1);
-            ptx::mbar_init(&empty[i], 1);
+            ptx::mbar_init(&empty[i], kCluster);   // every CTA of the cluster must have consumed the slot
         }
         for (int i = 0; i < kAccStages; ++i) {
             ptx::mbar_init(&acc_full[i], 1);
@@ -89,6 +174,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
     ptx::tc_fence_before();
     __syncthreads();
+    if (kCluster > 1) ptx::cluster_sync();   // peers' barriers exist before anyone multicasts into them
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -97,9 +183,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (ptx::elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile % m_tiles) * BM;
-                const int n_blk = tile / m_tiles;
+            for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
+                const int m0 = ((unit % m_groups) * kCluster + crank) * BM;
+                const int n_blk = unit / m_groups;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     ptx::mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * kStageBytes;
@@ -118,14 +204,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     }
                     if (kEpi == EPI_SWIGLU) {
                         // rows [0,128) of the B tile from w1, rows [128,256) from w3 (same row range of each)
-                        ptx::tma_load_2d(sb, &tmB, &full[stage], r0, n_blk * (BN / 2));
-                        ptx::tma_load_2d(sb + kBBytes / 2, &tmB2, &full[stage], r0, n_blk * (BN / 2));
+                        if (kCluster == 1) {
+                            ptx::tma_load_2d(sb, &tmB, &full[stage], r0, n_blk * (BN / 2));
+                            ptx::tma_load_2d(sb + kBBytes / 2, &tmB2, &full[stage], r0, n_blk * (BN / 2));
+                        } else {   // kCluster == 2: CTA 0 supplies the w1 half, CTA 1 the w3 half, to both CTAs
+                            ptx::tma_load_2d_mcast(sb + crank * (kBBytes / 2), crank == 0 ? &tmB : &tmB2, &full[stage], r0,
+                                                   n_blk * (BN / 2), kMask);
+                        }
                     } else if (!kBMn) {
-                        ptx::tma_load_2d(sb, mb, &full[stage], r0, n_blk * BN);         // box {64 r, 256 n}
+                        if (kCluster == 1) {
+                            ptx::tma_load_2d(sb, mb, &full[stage], r0, n_blk * BN);     // box {64 r, 256 n}
+                        } else {                                                        // box {64 r, 256/kCluster n}
+                            ptx::tma_load_2d_mcast(sb + crank * (kBBytes / kCluster), mb, &full[stage], r0,
+                                                   n_blk * BN + crank * (BN / kCluster), kMask);
+                        }
                     } else {
 #pragma unroll
-                        for (int j = 0; j < BN / 64; ++j)                               // boxes {64 n, 64 r}
-                            ptx::tma_load_2d(sb + j * (64 * BK * 2), mb, &full[stage], n_blk * BN + j * 64, r0);
+                        for (int j = 0; j < BN / 64; ++j) {                             // boxes {64 n, 64 r}
+                            if (kCluster == 1)
+                                ptx::tma_load_2d(sb + j * (64 * BK * 2), mb, &full[stage], n_blk * BN + j * 64, r0);
+                            else if (j % kCluster == crank)
+                                ptx::tma_load_2d_mcast(sb + j * (64 * BK * 2), mb, &full[stage], n_blk * BN + j * 64, r0, kMask);
+                        }
                     }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
@@ -140,7 +240,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         constexpr uint32_t kLboMn = 64 * BK * 2, kSbo = 1024;
         int stage = 0, acc = 0;
         uint32_t phase = 0, acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
             ptx::mbar_wait(&acc_empty[acc], acc_phase ^ 1);
             ptx::tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * BN;
@@ -160,7 +260,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                                  : ptx::umma_smem_desc(sb + k * 32, 0, kSbo);
                         ptx::umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0);
                     }
-                    ptx::umma_commit(&empty[stage]);                       // frees the smem slot when the MMAs retire
+                    // free the smem slot when the MMAs retire — in every CTA of the cluster, because the peers'
+                    // multicast writes land in this CTA's slot too
+                    if (kCluster == 1) ptx::umma_commit(&empty[stage]);
+                    else ptx::umma_commit_mcast(&empty[stage], kMask);
                     if (kb == num_kb - 1) ptx::umma_commit(&acc_full[acc]);  // accumulator ready
                 }
                 __syncwarp();
@@ -173,77 +276,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int q = warp & 3;                 // TMEM lane quarter this warp may read
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const int m0 = (tile % m_tiles) * BM;
-            const int n_blk = tile / m_tiles;
+        for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
+            const int m0 = ((unit % m_groups) * kCluster + crank) * BM;
+            const int n_blk = unit / m_groups;
             const int row = m0 + q * 32 + lane;
             ptx::mbar_wait(&acc_full[acc], acc_phase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
-            if (kEpi == EPI_SWIGLU) {
-                const int h0 = n_blk * (BN / 2);   // first hidden column of this tile
-                const int hidden = g.N / 2;
-#pragma unroll 1
-                for (int c = 0; c < BN / 2; c += 32) {
-                    uint32_t rg[32], ru[32];
-                    ptx::tmem_ld32(taddr + c, rg);
-                    ptx::tmem_ld32(taddr + BN / 2 + c, ru);
-                    ptx::tmem_ld_wait();
-                    if (row < g.M) {
-#pragma unroll
-                        for (int v = 0; v < 4; ++v) {
-                            const int col = h0 + c + v * 8;
-                            if (col < hidden) {
-                                float gt[8], up[8], act[8];
-#pragma unroll
-                                for (int j = 0; j < 8; ++j) {
-                                    gt[j] = round_bf16(__uint_as_float(rg[v * 8 + j]));
-                                    up[j] = round_bf16(__uint_as_float(ru[v * 8 + j]));
-                                    act[j] = round_bf16(gt[j] / (1.f + __expf(-gt[j]))) * up[j];
-                                }
-                                const int64_t off = (int64_t)row * g.ldc + col;
-                                st8(g.C + off, pack8(act));
-                                if (g.C_gate) st8(g.C_gate + off, pack8(gt));
-                                if (g.C_up) st8(g.C_up + off, pack8(up));
-                            }
-                        }
-                    }
-                }
-            } else {
-                const int n0 = n_blk * BN;
-#pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
-                    uint32_t r[32];
-                    ptx::tmem_ld32(taddr + c, r);
-                    ptx::tmem_ld_wait();
-                    if (row < g.M) {
-#pragma unroll
-                        for (int v = 0; v < 4; ++v) {
-                            const int col = n0 + c + v * 8;
-                            if (col < g.N) {
-                                float f[8];
-#pragma unroll
-                                for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
-                                if (kEpi == EPI_ROPE && col < g.rot_cols) {
-                                    const int pos = row % g.seq_len;
-                                    const int pair0 = (col % g.head_dim) >> 1;
-                                    const int64_t to = (int64_t)pos * (g.head_dim >> 1) + pair0;
-                                    const float4 cs = *reinterpret_cast<const float4*>(g.cos_t + to);
-                                    const float4 sn = *reinterpret_cast<const float4*>(g.sin_t + to);
-                                    const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
-#pragma unroll
-                                    for (int j = 0; j < 4; ++j) {
-                                        const float a = round_bf16(f[2 * j]), b = round_bf16(f[2 * j + 1]);
-                                        f[2 * j] = a * cc[j] - b * ss[j];
-                                        f[2 * j + 1] = a * ss[j] + b * cc[j];
-                                    }
-                                }
-                                st8(g.C + (int64_t)row * g.ldc + col, pack8(f));
-                            }
-                        }
-                    }
-                }
-            }
+            epilogue_tile<kEpi>(g, taddr, row, n_blk);
             // every TMEM read of this accumulator stage has completed (wait::ld above): hand it back
             ptx::tc_fence_before();
             __syncwarp();
@@ -253,7 +293,170 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     ptx::tc_fence_before();
     __syncthreads();
+    if (kCluster > 1) ptx::cluster_sync();   // no CTA leaves while a peer may still signal its barriers
     if (warp == 1) ptx::tmem_dealloc<512>(tmem_base);
+}
+
+
+// ------------------------------------------------------------------------------------------------------------
+// CTA-pair version (tcgen05 cta_group::2).  Two CTAs on the two SMs of a TPC compute one 256 x 256 tile: each
+// CTA keeps its own 128 rows of A and HALF of the B tile (128 of the 256 n-rows) in shared memory, the leader
+// CTA issues one M=256 UMMA per 16 reduction elements that reads A from both CTAs' shared memory and both B
+// halves, and each CTA's TMEM receives its 128 x 256 half of the accumulator.  Per CTA a k-block now costs
+// 32 KB of TMA writes and 8 KB of operand reads per UMMA instead of 48 KB / 12 KB, which is what lifts the
+// shared-memory-bandwidth ceiling of the single-CTA kernel; the stage is smaller, so the ring is 6 deep.
+//   full[s]   lives in the leader; both producers arrive on it (the peer through a cluster address) and both
+//             CTAs' TMA loads complete their bytes on it
+//   empty[s], acc_full[a]   one copy per CTA; the leader's tcgen05.commit is multicast to both
+//   acc_empty[a]            lives in the leader; 4 epilogue warps of each CTA arrive on it
+constexpr int kStages2 = 6;
+constexpr int kStageBytes2 = kABytes + kBBytes / 2;   // 32 KB
+constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + 1024 + 256;
+
+template <int kEpi, bool kAMn, bool kBMn>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                const GemmArgs g) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages2 * kStageBytes2);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + kStages2;
+    uint64_t* acc_full = bars + 2 * kStages2;
+    uint64_t* acc_empty = acc_full + kAccStages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + kAccStages);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int crank = (int)ptx::cluster_ctarank();
+    const bool leader = crank == 0;
+    const int m_pairs = (g.M + 2 * BM - 1) / (2 * BM);
+    const int n_tiles = (g.N + BN - 1) / BN;
+    const int num_units = m_pairs * n_tiles;
+    const int num_kb = (g.K + BK - 1) / BK;
+    const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmB);
+        for (int i = 0; i < kStages2; ++i) {
+            ptx::mbar_init(&full[i], 1);      // the leader's producer arms it for the bytes of BOTH CTAs' loads
+            ptx::mbar_init(&empty[i], 1);
+        }
+        for (int i = 0; i < kAccStages; ++i) {
+            ptx::mbar_init(&acc_full[i], 1);
+            ptx::mbar_init(&acc_empty[i], 8);  // 4 epilogue warps x 2 CTAs (used in the leader only)
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) ptx::tmem_alloc_2sm<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================= TMA producer (both CTAs) =================
+        if (ptx::elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int unit = pair_id; unit < num_units; unit += num_pairs) {
+                const int m0 = ((unit % m_pairs) * 2 + crank) * BM;
+                const int n_blk = unit / m_pairs;
+                const int n0 = n_blk * BN + crank * (BN / 2);     // this CTA's half of the B tile
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    ptx::mbar_wait(&empty[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * kStageBytes2;
+                    uint8_t* sb = sa + kABytes;
+                    // Both CTAs' TMA loads complete their bytes on the LEADER's barrier.  Only the leader arrives on it
+                    // (a plain CTA-scope arrive; a cluster-scope release here costs a MEMBAR.ALL.GPU per k-block).
+                    // The peer's bytes may land before the leader has armed the phase: the transaction count just
+                    // goes negative until expect_tx, and the phase cannot complete before the leader's arrive.
+                    const uint32_t fb = ptx::mapa(ptx::smem_u32(&full[stage]), 0);
+                    if (leader) ptx::mbar_arrive_expect_tx(&full[stage], 2 * kStageBytes2);
+                    const bool second = kb >= g.nk1;
+                    const CUtensorMap* ma = second ? &tmA2 : &tmA;
+                    const CUtensorMap* mb = second ? &tmB2 : &tmB;
+                    const int r0 = (second ? kb - g.nk1 : kb) * BK;
+                    if (!kAMn) {
+                        ptx::tma_load_2d_2sm(sa, ma, fb, r0, m0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j)
+                            ptx::tma_load_2d_2sm(sa + j * (64 * BK * 2), ma, fb, m0 + j * 64, r0);
+                    }
+                    if (kEpi == EPI_SWIGLU) {
+                        // accumulator columns [0,128) = gate (w1 rows, held by the leader), [128,256) = up (w3, peer)
+                        ptx::tma_load_2d_2sm(sb, leader ? &tmB : &tmB2, fb, r0, n_blk * (BN / 2));
+                    } else if (!kBMn) {
+                        ptx::tma_load_2d_2sm(sb, mb, fb, r0, n0);                        // box {64 r, 128 n}
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 2 / 64; ++j)                           // boxes {64 n, 64 r}
+                            ptx::tma_load_2d_2sm(sb + j * (64 * BK * 2), mb, fb, n0 + j * 64, r0);
+                    }
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer (leader CTA only) =================
+        if (leader) {
+            constexpr uint32_t idesc = ptx::umma_idesc_bf16(2 * BM, BN, kAMn, kBMn);
+            constexpr uint32_t kLboMn = 64 * BK * 2, kSbo = 1024;
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int unit = pair_id; unit < num_units; unit += num_pairs) {
+                ptx::mbar_wait(&acc_empty[acc], acc_phase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    ptx::mbar_wait(&full[stage], phase);
+                    ptx::tc_fence_after();
+                    if (ptx::elect_one()) {
+                        const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes2);
+                        const uint32_t sb = sa + kABytes;
+#pragma unroll
+                        for (int k = 0; k < BK / 16; ++k) {
+                            const uint64_t da = kAMn ? ptx::umma_smem_desc(sa + k * 16 * 128, kLboMn, kSbo)
+                                                     : ptx::umma_smem_desc(sa + k * 32, 0, kSbo);
+                            const uint64_t db = kBMn ? ptx::umma_smem_desc(sb + k * 16 * 128, kLboMn, kSbo)
+                                                     : ptx::umma_smem_desc(sb + k * 32, 0, kSbo);
+                            ptx::umma_bf16_2sm(tmem_d, da, db, idesc, (kb | k) != 0);
+                        }
+                        ptx::umma_commit_2sm(&empty[stage], 3);
+                        if (kb == num_kb - 1) ptx::umma_commit_2sm(&acc_full[acc], 3);
+                    }
+                    __syncwarp();
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+                if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ================= epilogue (both CTAs, own 128 rows) =================
+        const int q = warp & 3;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int unit = pair_id; unit < num_units; unit += num_pairs) {
+            const int m0 = ((unit % m_pairs) * 2 + crank) * BM;
+            const int n_blk = unit / m_pairs;
+            const int row = m0 + q * 32 + lane;
+            ptx::mbar_wait(&acc_full[acc], acc_phase);
+            ptx::tc_fence_after();
+            const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
+            epilogue_tile<kEpi>(g, taddr, row, n_blk);
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&acc_empty[acc]), 0));
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();
+    if (warp == 1) ptx::tmem_dealloc_2sm<512>(tmem_base);
 }
 
 // ------------------------------------------------------------------------------------------------ host
@@ -283,21 +486,86 @@ static int make_tmap(CUtensorMap* out, const void* ptr, int64_t rows, int64_t co
     return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
 }
 
-template <int kEpi, bool kAMn, bool kBMn>
-static int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2, const CUtensorMap& b2,
-                  const GemmArgs& g, int max_ctas, cudaStream_t stream) {
-    auto kern = gemm_tc_kernel<kEpi, kAMn, kBMn>;
+template <int kEpi, bool kAMn, bool kBMn, int kCluster>
+static int launch_c(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2, const CUtensorMap& b2,
+                    const GemmArgs& g, int max_ctas, cudaStream_t stream) {
+    auto kern = gemm_tc_kernel<kEpi, kAMn, kBMn, kCluster>;
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
-    const int tiles = ((g.M + BM - 1) / BM) * ((g.N + BN - 1) / BN);
+    const int m_tiles = (g.M + BM - 1) / BM, n_tiles = (g.N + BN - 1) / BN;
+    const int units = ((m_tiles + kCluster - 1) / kCluster) * n_tiles;
     int grid = max_ctas > 0 ? max_ctas : kNumSMs;
-    if (grid > tiles) grid = tiles;
-    kern<<<grid, kGemmThreads, kSmemBytes, stream>>>(a, b, a2, b2, g);
-    return (int)cudaGetLastError();
+    if (grid > units * kCluster) grid = units * kCluster;
+    grid = grid / kCluster * kCluster;
+    if (grid < kCluster) grid = kCluster;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kCluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return (int)cudaLaunchKernelEx(&cfg, kern, a, b, a2, b2, g);
+}
+
+template <int kEpi, bool kAMn, bool kBMn>
+static int launch_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2, const CUtensorMap& b2,
+                       const GemmArgs& g, int max_ctas, cudaStream_t stream) {
+    auto kern = gemm_tc2_kernel<kEpi, kAMn, kBMn>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2);
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const int units = ((g.M + 2 * BM - 1) / (2 * BM)) * ((g.N + BN - 1) / BN);
+    int grid = max_ctas > 0 ? max_ctas : kNumSMs;
+    if (grid > units * 2) grid = units * 2;
+    grid = grid / 2 * 2;
+    if (grid < 2) grid = 2;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = kSmemBytes2;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return (int)cudaLaunchKernelEx(&cfg, kern, a, b, a2, b2, g);
+}
+
+// cluster size used by the entry points (FTL_GEMM_CLUSTER=1 falls back to independent CTAs)
+static int gemm_cluster() {
+    static int c = -1;
+    if (c < 0) {
+        const char* e = getenv("FTL_GEMM_CLUSTER");
+        c = e ? atoi(e) : 0;   // 0 = CTA-pair kernel (cta_group::2); 1 / 2 / 4 = single-CTA MMA with that cluster size
+        if (c != 0 && c != 1 && c != 2 && c != 4) c = 0;
+    }
+    return c;
+}
+
+template <int kEpi, bool kAMn, bool kBMn>
+static int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2, const CUtensorMap& b2,
+                  const GemmArgs& g, int max_ctas, cudaStream_t stream) {
+    const int c = gemm_cluster();
+    if (c == 0) return launch_pair<kEpi, kAMn, kBMn>(a, b, a2, b2, g, max_ctas, stream);
+    if (c == 1) return launch_c<kEpi, kAMn, kBMn, 1>(a, b, a2, b2, g, max_ctas, stream);
+    if (c == 4 && kEpi != EPI_SWIGLU) return launch_c<kEpi, kAMn, kBMn, 4>(a, b, a2, b2, g, max_ctas, stream);
+    return launch_c<kEpi, kAMn, kBMn, 2>(a, b, a2, b2, g, max_ctas, stream);
 }
 
 }  // namespace ftl
@@ -317,14 +585,15 @@ FTL_API int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, i
     int e;
     e = a_mn ? make_tmap(&ta, a, K, M, lda, 64, BK) : make_tmap(&ta, a, M, K, lda, BK, BM);
     if (e) return e;
-    e = b_mn ? make_tmap(&tb, b, K, N, ldb, 64, BK) : make_tmap(&tb, b, N, K, ldb, BK, BN);
+    const int cl = gemm_cluster() == 0 ? 2 : gemm_cluster();
+    e = b_mn ? make_tmap(&tb, b, K, N, ldb, 64, BK) : make_tmap(&tb, b, N, K, ldb, BK, BN / cl);
     if (e) return e;
     ta2 = ta;
     tb2 = tb;
     if (K2 > 0) {
         e = a_mn ? make_tmap(&ta2, a2, K2, M, lda2, 64, BK) : make_tmap(&ta2, a2, M, K2, lda2, BK, BM);
         if (e) return e;
-        e = b_mn ? make_tmap(&tb2, b2, K2, N, ldb2, 64, BK) : make_tmap(&tb2, b2, N, K2, ldb2, BK, BN);
+        e = b_mn ? make_tmap(&tb2, b2, K2, N, ldb2, 64, BK) : make_tmap(&tb2, b2, N, K2, ldb2, BK, BN / cl);
         if (e) return e;
     }
     GemmArgs g{};
@@ -364,7 +633,7 @@ FTL_API int ftl_gemm_qkv_rope(const void* x, int64_t ldx, const void* wqkv, int6
     CUtensorMap ta, tb;
     int e;
     if ((e = make_tmap(&ta, x, M, K, ldx, BK, BM))) return e;
-    if ((e = make_tmap(&tb, wqkv, N, K, ldw, BK, BN))) return e;
+    if ((e = make_tmap(&tb, wqkv, N, K, ldw, BK, BN / (gemm_cluster() == 0 ? 2 : gemm_cluster())))) return e;
     GemmArgs g{};
     g.C = (__nv_bfloat16*)qkv; g.ldc = ldo;
     g.M = M; g.N = N; g.K = K; g.nk1 = (K + BK - 1) / BK;

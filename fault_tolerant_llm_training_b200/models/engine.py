@@ -18,6 +18,7 @@ enabled for that shape; attention uses the library SDPA until csrc/attn_*.cu cov
 from __future__ import annotations
 
 import math
+import os
 from typing import List, Optional
 
 import torch
@@ -226,18 +227,28 @@ class NativeEngine:
                 self.hook_params(self._params_waited)
 
     # ---- GEMM dispatch: C = A @ B^T (nt), A @ B (nn), A^T @ B (tn) -------------------------------
-    @staticmethod
-    def gemm_nt(a, b, out):
+    # FTL_GEMM=tc (default): the hand-written tcgen05 CTA-pair kernel of csrc/gemm_tc.cu for every GEMM of the
+    # step, with the RoPE / SwiGLU epilogues and the split reduction fused (0.97-1.20x cuBLAS on these shapes,
+    # profiles/gemm_tc_pair_vs_cublas.jsonl).  FTL_GEMM=cublas: library GEMMs + separate elementwise kernels.
+    USE_TC = os.environ.get("FTL_GEMM", "tc") != "cublas"
+
+    def gemm_nt(self, a, b, out):
+        if self.USE_TC:
+            return N.gemm(a, b, out)
         return torch.mm(a, b.t(), out=out)
 
-    @staticmethod
-    def gemm_nn(a, b, out, accumulate=False):
-        if accumulate:
-            return torch.addmm(out, a, b, out=out)
-        return torch.mm(a, b, out=out)
+    def gemm_nn(self, a, b, out, a2=None, b2=None):
+        """out = a @ b (+ a2 @ b2)."""
+        if self.USE_TC:
+            return N.gemm(a, b, out, b_mn=True, a2=a2, b2=b2)
+        torch.mm(a, b, out=out)
+        if a2 is not None:
+            torch.addmm(out, a2, b2, out=out)
+        return out
 
-    @staticmethod
-    def gemm_tn(a, b, out):
+    def gemm_tn(self, a, b, out):
+        if self.USE_TC:
+            return N.gemm(a, b, out, a_mn=True, b_mn=True)
         return torch.mm(a.t(), b, out=out)
 
     # ---- attention (library SDPA island; replaced by csrc/attn when available) -------------------
@@ -278,16 +289,22 @@ class NativeEngine:
             self._need(i + 2)   # this layer, and the norm weight of the next one (or the head) used by the fused norm
             if i == 0:
                 N.rmsnorm_fwd(self.x[0], lw["wan"], c.norm_eps, self.xn[0], self.rstd1[0])
-            self.gemm_nt(self.xn[i], lw["wqkv"], self.qkv[i])
-            N.rope_inplace(self.qkv[i], self.cos, self.sin, self.S, rot, hd)
+            if self.USE_TC:   # QKV projection with RoPE in the GEMM epilogue (K3 + K4)
+                N.gemm_qkv_rope(self.xn[i], lw["wqkv"], self.qkv[i], self.cos, self.sin, self.S, hd, rot)
+            else:
+                self.gemm_nt(self.xn[i], lw["wqkv"], self.qkv[i])
+                N.rope_inplace(self.qkv[i], self.cos, self.sin, self.S, rot, hd)
             a = self._attention_fwd(i)
             self.attn_flat = a
             self.gemm_nt(a, lw["wo"], self.ao)
             # h = x + attn_out ; hn = norm(h)
             N.rmsnorm_fwd(self.x[i], lw["wfn"], c.norm_eps, self.hn[i], self.rstd2[i], delta=self.ao, h_out=self.h[i])
-            self.gemm_nt(self.hn[i], lw["ww1"], self.gate[i])
-            self.gemm_nt(self.hn[i], lw["ww3"], self.up[i])
-            N.swiglu_fwd(self.gate[i], self.up[i], self.act[i])
+            if self.USE_TC:   # gate|up dual GEMM with the SwiGLU epilogue (K9 + K10)
+                N.gemm_swiglu(self.hn[i], lw["ww1"], lw["ww3"], self.act[i], self.gate[i], self.up[i])
+            else:
+                self.gemm_nt(self.hn[i], lw["ww1"], self.gate[i])
+                self.gemm_nt(self.hn[i], lw["ww3"], self.up[i])
+                N.swiglu_fwd(self.gate[i], self.up[i], self.act[i])
             self.gemm_nt(self.act[i], lw["ww2"], self.ff)
             # x_{i+1} = h + ff ; next norm (attention_norm of layer i+1, or the final norm)
             if i + 1 < c.n_layers:
@@ -322,8 +339,7 @@ class NativeEngine:
             N.swiglu_bwd(self.dact, self.gate[i], self.up[i], self.dgate, self.dup)
             self.gemm_tn(self.dgate, self.hn[i], lw["gw1"])
             self.gemm_tn(self.dup, self.hn[i], lw["gw3"])
-            self.gemm_nn(self.dgate, lw["ww1"], self.dtmp)
-            self.gemm_nn(self.dup, lw["ww3"], self.dtmp, accumulate=True)
+            self.gemm_nn(self.dgate, lw["ww1"], self.dtmp, a2=self.dup, b2=lw["ww3"])   # one pass over K = 2F
             # dh = dx + d ffn_norm
             N.rmsnorm_bwd(self.dtmp, self.h[i], lw["wfn"], self.rstd2[i], self.dh, lw["gfn"], self.norm_scratch,
                           dres=dx)
