@@ -169,6 +169,53 @@ dp_adamw_allgather_kernel(__nv_bfloat16* const* __restrict__ peer_p, const __nv_
     }
 }
 
+// Plain parameter all-gather (N13): dst[r * n : (r+1) * n] = owner r's shard (n elements at `off` in its compact
+// buffer), for r = 0..W-1, through 16-byte peer loads.  Used for the operands whose gather is not fused into a GEMM.
+template <int W>
+__global__ void __launch_bounds__(512)
+fsdp_gather_kernel(const __nv_bfloat16* const* __restrict__ peer_shards, int64_t off, __nv_bfloat16* __restrict__ dst,
+                   int64_t nvec, int rank, const uint32_t* __restrict__ status) {
+    if (*status != 0) return;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec * W; i += (int64_t)gridDim.x * blockDim.x) {
+        const int rr = (int)(i / nvec);
+        const int r = (rr + rank) % W;                     // start with the own shard, peers rotate
+        const int64_t k = i - (int64_t)rr * nvec;
+        const int4 v = ld_peer16(peer_shards[r] + off + k * 8);
+        *reinterpret_cast<int4*>(dst + ((int64_t)r * nvec + k) * 8) = v;
+    }
+}
+
+// AdamW on one compact shard (FSDP): p, m, v are shard-local, g points at the reduced gradient range.
+__global__ void __launch_bounds__(512)
+adamw_shard_kernel(__nv_bfloat16* __restrict__ p, const __nv_bfloat16* __restrict__ g, __nv_bfloat16* __restrict__ m,
+                   __nv_bfloat16* __restrict__ v, int64_t nvec, const float* __restrict__ hyper,
+                   const float* __restrict__ stats, const uint32_t* __restrict__ status,
+                   unsigned long long* __restrict__ commits) {
+    if (*status != 0 || stats[2] == 0.f) return;
+    if (commits && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(commits, 1ull);
+    const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4];
+    const float bc1 = hyper[5], bc2_sqrt = hyper[6], coef = stats[1];
+    const float step_size = lr / bc1, decay = 1.f - lr * wd;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+        float pf[8], gf[8], mf[8], vf[8];
+        unpack8(ld8_stream(p + i * 8), pf);
+        unpack8(ld8_stream(g + i * 8), gf);
+        unpack8(ld8_stream(m + i * 8), mf);
+        unpack8(ld8_stream(v + i * 8), vf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float gr = gf[j] * coef;
+            mf[j] = mf[j] + (1.f - b1) * (gr - mf[j]);
+            vf[j] = b2 * vf[j] + (1.f - b2) * gr * gr;
+            const float denom = sqrtf(vf[j]) / bc2_sqrt + eps;
+            pf[j] = pf[j] * decay - step_size * (mf[j] / denom);
+        }
+        st8_stream(p + i * 8, pack8(pf));
+        st8_stream(m + i * 8, pack8(mf));
+        st8_stream(v + i * 8, pack8(vf));
+    }
+}
+
 static inline int comm_grid(int64_t nvec, int max_ctas) {
     int64_t blocks = (nvec + 511) / 512;
     int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)kNumSMs * 4;
@@ -256,6 +303,31 @@ FTL_API int ftl_dp_adamw_allgather(void* const* peer_p, const void* g, void* m, 
     switch (world) { AG_CASE(1) AG_CASE(2) AG_CASE(3) AG_CASE(4) AG_CASE(5) AG_CASE(6) AG_CASE(7) AG_CASE(8)
         default: return (int)cudaErrorInvalidValue; }
 #undef AG_CASE
+    FTL_LAUNCH_CHECK();
+    return 0;
+}
+
+
+FTL_API int ftl_fsdp_gather(const void* const* peer_shards, int64_t off, void* dst, int64_t n_per_rank, int rank, int world,
+                            const void* status, int max_ctas, cudaStream_t stream) {
+    if (off % 8 || n_per_rank % 8 || n_per_rank <= 0) return (int)cudaErrorInvalidValue;
+    const int grid = comm_grid(n_per_rank / 8 * world, max_ctas);
+    auto P = (const __nv_bfloat16* const*)peer_shards;
+    auto S = (const uint32_t*)status;
+#define FG_CASE(W) case W: fsdp_gather_kernel<W><<<grid, 512, 0, stream>>>(P, off, (__nv_bfloat16*)dst, n_per_rank / 8, rank, S); break;
+    switch (world) { FG_CASE(1) FG_CASE(2) FG_CASE(3) FG_CASE(4) FG_CASE(5) FG_CASE(6) FG_CASE(7) FG_CASE(8)
+        default: return (int)cudaErrorInvalidValue; }
+#undef FG_CASE
+    FTL_LAUNCH_CHECK();
+    return 0;
+}
+
+FTL_API int ftl_adamw_shard(void* p, const void* g, void* m, void* v, int64_t n, const float* hyper, const float* stats,
+                            const void* status, void* commits, int max_ctas, cudaStream_t stream) {
+    if (n % 8 || n <= 0) return (int)cudaErrorInvalidValue;
+    adamw_shard_kernel<<<comm_grid(n / 8, max_ctas), 512, 0, stream>>>(
+        (__nv_bfloat16*)p, (const __nv_bfloat16*)g, (__nv_bfloat16*)m, (__nv_bfloat16*)v, n / 8, hyper, stats,
+        (const uint32_t*)status, (unsigned long long*)commits);
     FTL_LAUNCH_CHECK();
     return 0;
 }

@@ -53,7 +53,69 @@ struct GemmArgs {
     int M, N, K;            // N counts accumulator columns (SWIGLU: 2 x hidden)
     int nk1;                // k-blocks served by the first (A, B) pair; the rest come from the second
     int seq_len, head_dim, rot_cols;
+    // ---- fused parameter all-gather (FSDP): the B operand is row-sharded over `world` ranks; this kernel pulls the
+    // shards out of the owners' memory over NVLink into the local staging copy that its own TMA loads then read.
+    // Work item = 16 rows of one 128-row half block; the epilogue warps of every CTA take items from a counter
+    // while they wait for an accumulator, so the transfer rides along with the MMAs instead of preceding them.
+    const __nv_bfloat16* const* gather_src;  // [world] base pointers of the owners' compact shard buffers (null = off)
+    __nv_bfloat16* gather_dst[2];            // local [rows, K] destination(s): B (and B2 for the SwiGLU pair)
+    int64_t gather_off[2];                   // element offset of this matrix' shard inside every owner's buffer
+    int gather_rows_per_rank;                // rows of each matrix owned by one rank (multiple of 128)
+    int gather_nmat;                         // 1, or 2 for SwiGLU (w1, w3)
+    int rank, world;
+    int* gather_next;                        // [1]  item dispenser      (zeroed before the launch)
+    int* gather_done;                        // [nmat * N/128] slices finished per half block (zeroed before launch)
 };
+
+constexpr int kGatherSliceRows = 16, kGatherSlices = 128 / kGatherSliceRows;
+
+// Copy one work item (kGatherSliceRows rows of B) from its owner to the local staging matrix.  One warp per item.
+__device__ __forceinline__ bool gather_one_item(const GemmArgs& g, int lane) {
+    const int halves = (g.gather_nmat == 2 ? g.N / 2 : g.N) / 128;           // half blocks per matrix
+    const int total = halves * g.gather_nmat * kGatherSlices;
+    int it = 0;
+    if (lane == 0) it = atomicAdd(g.gather_next, 1);
+    it = __shfl_sync(0xffffffffu, it, 0);
+    if (it >= total) return false;
+    const int slice = it % kGatherSlices;
+    const int mat = (it / kGatherSlices) % g.gather_nmat;
+    const int hpr = g.gather_rows_per_rank / 128;                             // half blocks per rank
+    const int hb = ((it / kGatherSlices) / g.gather_nmat + g.rank * hpr) % halves;   // own shard first, then rotate
+    const int owner = hb / hpr;
+    const int64_t row_in_shard = (int64_t)(hb % hpr) * 128 + slice * kGatherSliceRows;
+    const int4* src = reinterpret_cast<const int4*>(g.gather_src[owner] + g.gather_off[mat] + row_in_shard * g.K);
+    int4* dst = reinterpret_cast<int4*>(g.gather_dst[mat] + ((int64_t)hb * 128 + slice * kGatherSliceRows) * g.K);
+    const int nvec = kGatherSliceRows * g.K / 8;
+    int i = lane;
+    for (; i + 7 * 32 < nvec; i += 8 * 32) {   // 8 independent 16-byte peer loads in flight per lane
+        int4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            asm volatile("ld.global.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + i + u * 32));
+#pragma unroll
+        for (int u = 0; u < 8; ++u) dst[i + u * 32] = v[u];
+    }
+    for (; i < nvec; i += 32) dst[i] = src[i];
+    __threadfence();                           // the slice is visible device-wide before it is counted
+    __syncwarp();
+    if (lane == 0) atomicAdd(g.gather_done + mat * halves + hb, 1);
+    return true;
+}
+
+// Producer side: block until every slice of half block `hb` of matrix `mat` has landed, then make those generic-proxy
+// writes visible to the TMA (async proxy) loads that follow.
+__device__ __forceinline__ void gather_wait(const GemmArgs& g, int mat, int hb) {
+    const int halves = (g.gather_nmat == 2 ? g.N / 2 : g.N) / 128;
+    const int* flag = g.gather_done + mat * halves + hb;
+    int v;
+    const uint64_t t0 = ptx::global_timer_ns();
+    do {
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v < kGatherSlices && ptx::global_timer_ns() - t0 > 4000000000ull) __trap();
+    } while (v < kGatherSlices);
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+}
 
 // One thread = one output row of the tile: TMEM (32 fp32 columns at a time) -> registers -> fused math -> 16-byte
 // global stores.  taddr addresses this warp's TMEM lane quarter of the accumulator stage.
@@ -335,6 +397,9 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int num_units = m_pairs * n_tiles;
     const int num_kb = (g.K + BK - 1) / BK;
     const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    // with a fused gather, walk the n blocks starting at this rank's own shard: local rows need no NVLink traffic, and
+    // the ranks then pull from different owners at any moment
+    const int n_rot = g.gather_src ? (g.rank * n_tiles) / g.world : 0;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
@@ -363,8 +428,13 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             uint32_t phase = 0;
             for (int unit = pair_id; unit < num_units; unit += num_pairs) {
                 const int m0 = ((unit % m_pairs) * 2 + crank) * BM;
-                const int n_blk = unit / m_pairs;
+                const int n_blk = (unit / m_pairs + n_rot) % n_tiles;
                 const int n0 = n_blk * BN + crank * (BN / 2);     // this CTA's half of the B tile
+                if (g.gather_src) {
+                    // this CTA's B half must have been gathered before TMA reads it
+                    if (kEpi == EPI_SWIGLU) gather_wait(g, crank, n_blk);
+                    else gather_wait(g, 0, n_blk * 2 + crank);
+                }
                 for (int kb = 0; kb < num_kb; ++kb) {
                     ptx::mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * kStageBytes2;
@@ -439,10 +509,13 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int q = warp & 3;
         int acc = 0;
         uint32_t acc_phase = 0;
+        bool gather_left = g.gather_src != nullptr;
         for (int unit = pair_id; unit < num_units; unit += num_pairs) {
             const int m0 = ((unit % m_pairs) * 2 + crank) * BM;
-            const int n_blk = unit / m_pairs;
+            const int n_blk = (unit / m_pairs + n_rot) % n_tiles;
             const int row = m0 + q * 32 + lane;
+            // while the accumulator is not ready, move parameter slices (fused all-gather)
+            while (gather_left && !ptx::mbar_try_wait(&acc_full[acc], acc_phase)) gather_left = gather_one_item(g, lane);
             ptx::mbar_wait(&acc_full[acc], acc_phase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
@@ -452,6 +525,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&acc_empty[acc]), 0));
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
+        while (gather_left) gather_left = gather_one_item(g, lane);   // CTAs without tiles still help
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -639,4 +713,60 @@ FTL_API int ftl_gemm_qkv_rope(const void* x, int64_t ldx, const void* wqkv, int6
     g.M = M; g.N = N; g.K = K; g.nk1 = (K + BK - 1) / BK;
     g.cos_t = cos_t; g.sin_t = sin_t; g.seq_len = seq_len; g.head_dim = head_dim; g.rot_cols = rot_cols;
     return launch<EPI_ROPE, false, false>(ta, tb, ta, tb, g, max_ctas, stream);
+}
+
+
+// ---- FSDP: the same two fused GEMMs with the parameter all-gather of their weight operand pulled into the kernel ----
+// peer_shards: device array [world] of the owners' compact shard buffers; shard_off*: element offset of the matrix'
+// shard in each of them; rows_per_rank: rows owned by each rank (multiple of 128).  The full [rows, K] matrix is
+// assembled in `wqkv` / `w1`, `w3` (local staging) while the MMAs run.  scratch: >= 1 + n_mat * rows/128 ints.
+static int gather_setup(GemmArgs& g, const void* const* peer_shards, int nmat, void* dst0, void* dst1, int64_t off0,
+                        int64_t off1, int rows, int rows_per_rank, int rank, int world, int* scratch, cudaStream_t stream) {
+    if (gemm_cluster() != 0 || rows_per_rank % 128 || rows % 128 || rows_per_rank * world != rows) return (int)cudaErrorInvalidValue;
+    const int halves = rows / 128;
+    cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(int) * (1 + nmat * halves), stream);
+    if (e != cudaSuccess) return (int)e;
+    g.gather_src = (const __nv_bfloat16* const*)peer_shards;
+    g.gather_dst[0] = (__nv_bfloat16*)dst0; g.gather_dst[1] = (__nv_bfloat16*)dst1;
+    g.gather_off[0] = off0; g.gather_off[1] = off1;
+    g.gather_rows_per_rank = rows_per_rank; g.gather_nmat = nmat; g.rank = rank; g.world = world;
+    g.gather_next = scratch; g.gather_done = scratch + 1;
+    return 0;
+}
+
+FTL_API int ftl_gemm_qkv_rope_gather(const void* x, int64_t ldx, void* wqkv, int64_t ldw, void* qkv, int64_t ldo,
+                                     const float* cos_t, const float* sin_t, int M, int N, int K, int seq_len, int head_dim,
+                                     int rot_cols, const void* const* peer_shards, int64_t shard_off, int rows_per_rank,
+                                     int rank, int world, int* scratch, cudaStream_t stream) {
+    if (M <= 0 || N <= 0 || K <= 0 || (N % 128) || (ldo % 8) || (ldx % 8) || ldw != K || (head_dim % 8) || (rot_cols % 8))
+        return (int)cudaErrorInvalidValue;
+    CUtensorMap ta, tb;
+    int e;
+    if ((e = make_tmap(&ta, x, M, K, ldx, BK, BM))) return e;
+    if ((e = make_tmap(&tb, wqkv, N, K, ldw, BK, BN / 2))) return e;
+    GemmArgs g{};
+    g.C = (__nv_bfloat16*)qkv; g.ldc = ldo;
+    g.M = M; g.N = N; g.K = K; g.nk1 = (K + BK - 1) / BK;
+    g.cos_t = cos_t; g.sin_t = sin_t; g.seq_len = seq_len; g.head_dim = head_dim; g.rot_cols = rot_cols;
+    if ((e = gather_setup(g, peer_shards, 1, wqkv, nullptr, shard_off, 0, N, rows_per_rank, rank, world, scratch, stream))) return e;
+    return launch_pair<EPI_ROPE, false, false>(ta, tb, ta, tb, g, 0, stream);
+}
+
+FTL_API int ftl_gemm_swiglu_gather(const void* x, int64_t ldx, void* w1, void* w3, int64_t ldw, void* act, void* gate,
+                                   void* up, int64_t ldo, int M, int H, int K, const void* const* peer_shards,
+                                   int64_t shard_off_w1, int64_t shard_off_w3, int rows_per_rank, int rank, int world,
+                                   int* scratch, cudaStream_t stream) {
+    if (M <= 0 || H <= 0 || K <= 0 || (H % 128) || (ldo % 8) || (ldx % 8) || ldw != K) return (int)cudaErrorInvalidValue;
+    CUtensorMap ta, tb, tb2;
+    int e;
+    if ((e = make_tmap(&ta, x, M, K, ldx, BK, BM))) return e;
+    if ((e = make_tmap(&tb, w1, H, K, ldw, BK, BN / 2))) return e;
+    if ((e = make_tmap(&tb2, w3, H, K, ldw, BK, BN / 2))) return e;
+    GemmArgs g{};
+    g.C = (__nv_bfloat16*)act; g.C_gate = (__nv_bfloat16*)gate; g.C_up = (__nv_bfloat16*)up;
+    g.ldc = ldo;
+    g.M = M; g.N = 2 * H; g.K = K; g.nk1 = (K + BK - 1) / BK;
+    if ((e = gather_setup(g, peer_shards, 2, w1, w3, shard_off_w1, shard_off_w3, H, rows_per_rank, rank, world, scratch, stream)))
+        return e;
+    return launch_pair<EPI_SWIGLU, false, false>(ta, tb, ta, tb2, g, 0, stream);
 }

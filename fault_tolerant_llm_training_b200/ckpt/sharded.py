@@ -68,15 +68,6 @@ class FlatCheckpointer:
         self._pending: Optional[Tuple[str, str, str]] = None
         N.ckpt_init(256 << 20)  # staging is allocated up front: the exit path must not depend on free memory
 
-    # -- which flat ranges this rank writes ---------------------------------------------------------------
-    def owned_ranges(self) -> List[Tuple[str, int, int]]:
-        # moments: exactly the ranges this rank maintains.  Parameters are replicated; each rank writes the same
-        # ranges of them, so the file system sees W parallel writers of 1/W each.
-        out = []
-        for lo, hi in self.t._moment_ranges():
-            out += [("p", lo, hi), ("m", lo, hi), ("v", lo, hi)]
-        return out
-
     # -- save ---------------------------------------------------------------------------------------------------
     def save(self, checkpoint_path: str, jobid: str, model, optimizer, lr_scheduler, training_step: int, *,
              data_state=None, rank: int = 0, world_size: int = 1, extra=None, logger=None) -> str:
@@ -90,11 +81,11 @@ class FlatCheckpointer:
                 shutil.rmtree(d)
             os.makedirs(d, exist_ok=True)
         env.barrier()
-        bufs = {"p": t.flat.p, "m": t.flat.m, "v": t.flat.v}
         segs, my_entries, off = [], [], 0
-        for name, lo, hi in self.owned_ranges():
+        for name, lo, hi, piece in t.checkpoint_segments():
             nbytes = (hi - lo) * 2
-            segs.append((bufs[name].data_ptr() + lo * 2, nbytes, off))
+            assert piece.numel() == hi - lo and piece.is_contiguous()
+            segs.append((piece.data_ptr(), nbytes, off))
             my_entries.append({"rank": env.rank, "buffer": name, "lo": lo, "hi": hi, "file": f"rank{env.rank}.bin",
                                "offset": off})
             off = (off + nbytes + ALIGN - 1) // ALIGN * ALIGN
@@ -153,7 +144,7 @@ def read_manifest(d: str) -> dict:
         return json.load(f)
 
 
-def _intersections(manifest: dict, buffer: str, lo: int, hi: int):
+def _intersections(manifest: dict, buffer: str, lo: int, hi: int, allow_gaps: bool = False):
     """(file, file_byte_offset, dst_element_offset, n_elements) pieces covering [lo, hi) of `buffer`."""
     out, covered = [], 0
     for s in manifest["segments"]:
@@ -163,7 +154,7 @@ def _intersections(manifest: dict, buffer: str, lo: int, hi: int):
         if a < b:
             out.append((s["file"], s["offset"] + (a - s["lo"]) * 2, a - lo, b - a))
             covered += b - a
-    if covered != hi - lo:
+    if covered != hi - lo and not allow_gaps:
         raise ValueError(f"shards do not cover {buffer}[{lo}:{hi}] (covered {covered} elements)")
     return out
 
@@ -180,12 +171,12 @@ def read_range_to_device(d: str, manifest: dict, buffer: str, lo: int, hi: int, 
 def read_flat_host(d: str, manifest: dict, buffer: str) -> torch.Tensor:
     """Whole flat buffer as a CPU bf16 tensor; zero-copy (mmap) when one file holds all of it."""
     n = manifest["flat_numel"]
-    pieces = _intersections(manifest, buffer, 0, n)
-    if len(pieces) == 1:
+    pieces = _intersections(manifest, buffer, 0, n, allow_gaps=True)   # alignment padding between tensors is not stored
+    if len(pieces) == 1 and pieces[0][3] == n:
         fname, foff, _, cnt = pieces[0]
         mm = np.memmap(os.path.join(d, fname), dtype=np.uint16, mode="r", offset=foff, shape=(cnt,))
         return torch.from_numpy(mm).view(torch.bfloat16)
-    out = torch.empty(n, dtype=torch.bfloat16)
+    out = torch.zeros(n, dtype=torch.bfloat16)
     raw = out.view(torch.int16).numpy().view(np.uint16)
     for fname, foff, doff, cnt in pieces:
         raw[doff:doff + cnt] = np.memmap(os.path.join(d, fname), dtype=np.uint16, mode="r", offset=foff, shape=(cnt,))

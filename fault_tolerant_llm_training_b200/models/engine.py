@@ -56,6 +56,19 @@ class FlatState:
                 prm.grad = self.g[off:off + n].view(shape)
                 self.index[name] = (off, n, shape)
 
+    # views used by the engine; the fully-sharded state overrides the parameter ones (weights live in staging slots)
+    def param_view(self, name: str) -> torch.Tensor:
+        return self.view(self.p, name)
+
+    def grad_view(self, name: str) -> torch.Tensor:
+        return self.view(self.g, name)
+
+    def param_span(self, first: str, last: str, shape) -> torch.Tensor:
+        return self.span(self.p, first, last, shape)
+
+    def grad_span(self, first: str, last: str, shape) -> torch.Tensor:
+        return self.span(self.g, first, last, shape)
+
     def view(self, buf: torch.Tensor, name: str) -> torch.Tensor:
         off, n, shape = self.index[name]
         return buf[off:off + n].view(shape)
@@ -85,9 +98,10 @@ class FlatAdamW(torch.optim.Optimizer):
         self.flat = flat
         self.steps_done = 0
         self._names = [n for n, _ in model.named_parameters()]
-        for name, prm in zip(self._names, self.param_groups[0]["params"]):
-            self.state[prm] = {"step": torch.tensor(0.0, dtype=torch.float32),
-                               "exp_avg": flat.view(flat.m, name), "exp_avg_sq": flat.view(flat.v, name)}
+        if flat.m.numel():   # the fully-sharded engine keeps only compact moment shards (no per-parameter views)
+            for name, prm in zip(self._names, self.param_groups[0]["params"]):
+                self.state[prm] = {"step": torch.tensor(0.0, dtype=torch.float32),
+                                   "exp_avg": flat.view(flat.m, name), "exp_avg_sq": flat.view(flat.v, name)}
 
     def hyper_values(self, max_norm: float) -> List[float]:
         """hyper[8] for the step about to be taken (step count t = steps_done + 1)."""
@@ -198,27 +212,29 @@ class NativeEngine:
         self.cos = model.rope_cos[:seq].to(device=device, dtype=torch.float32).contiguous()
         self.sin = model.rope_sin[:seq].to(device=device, dtype=torch.float32).contiguous()
         # weight views
-        fv, P, G = flat.view, flat.p, flat.g
-        self.w_emb, self.g_emb = fv(P, "tok_embeddings.weight"), fv(G, "tok_embeddings.weight")
-        self.w_out, self.g_out = fv(P, "output.weight"), fv(G, "output.weight")
-        self.w_fn, self.g_fn = fv(P, "norm.weight"), fv(G, "norm.weight")
+        pv, gv = flat.param_view, flat.grad_view
+        self.w_emb, self.g_emb = pv("tok_embeddings.weight"), gv("tok_embeddings.weight")
+        self.w_out, self.g_out = pv("output.weight"), gv("output.weight")
+        self.w_fn, self.g_fn = pv("norm.weight"), gv("norm.weight")
         self.lw = []
         for i in range(L):
             b = f"layers.{i}."
             names = dict(q=b + "attention.wq.weight", v=b + "attention.wv.weight", o=b + "attention.wo.weight",
                          w1=b + "feed_forward.w1.weight", w2=b + "feed_forward.w2.weight",
                          w3=b + "feed_forward.w3.weight", an=b + "attention_norm.weight", fn=b + "ffn_norm.weight")
-            lw = {}
-            for buf, tag in ((P, "w"), (G, "g")):
-                lw[tag + "qkv"] = flat.span(buf, names["q"], names["v"], (self.qkv_dim, d))
-                for k in ("o", "w1", "w2", "w3", "an", "fn"):
-                    lw[tag + k] = fv(buf, names[k])
+            lw = {"wqkv": flat.param_span(names["q"], names["v"], (self.qkv_dim, d)),
+                  "gqkv": flat.grad_span(names["q"], names["v"], (self.qkv_dim, d))}
+            for k in ("o", "w1", "w2", "w3", "an", "fn"):
+                lw["w" + k], lw["g" + k] = pv(names[k]), gv(names[k])
             self.lw.append(lw)
         # Pipelining hooks (parallel/pipeline.py).  Buckets: 0 = embedding, 1+i = layer i, L+1 = final norm + head.
         #   hook_params(b): called before the first kernel that reads bucket b's parameters
         #   hook_grads(b):  called after the last kernel that writes bucket b's gradients
         self.hook_params = None
         self.hook_grads = None
+        self.hook_params_bwd = None   # called before the backward of bucket b reads its parameters
+        self.fused_gather = None      # FSDP: object with qkv(i, x, out) / swiglu(i, x, act, gate, up) running the
+                                      # gather-fused GEMMs for layer i (parallel/fsdp.py)
 
     def _need(self, upto: int) -> None:
         if self.hook_params is not None:
@@ -286,33 +302,36 @@ class NativeEngine:
         self._need(0)
         N.embedding_fwd(tokens.view(-1), self.w_emb, self.x[0])
         for i, lw in enumerate(self.lw):
-            self._need(i + 2)   # this layer, and the norm weight of the next one (or the head) used by the fused norm
+            self._need(i + 1)
+            # residual add of the previous block fused with this block's attention_norm (x_i = h_{i-1} + ff)
             if i == 0:
                 N.rmsnorm_fwd(self.x[0], lw["wan"], c.norm_eps, self.xn[0], self.rstd1[0])
-            if self.USE_TC:   # QKV projection with RoPE in the GEMM epilogue (K3 + K4)
+            else:
+                N.rmsnorm_fwd(self.h[i - 1], lw["wan"], c.norm_eps, self.xn[i], self.rstd1[i], delta=self.ff, h_out=self.x[i])
+            if self.fused_gather is not None:   # FSDP: wq|wk|wv arrive over NVLink inside the GEMM (N12)
+                self.fused_gather.qkv(i, self.xn[i], self.qkv[i])
+            elif self.USE_TC:   # QKV projection with RoPE in the GEMM epilogue (K3 + K4)
                 N.gemm_qkv_rope(self.xn[i], lw["wqkv"], self.qkv[i], self.cos, self.sin, self.S, hd, rot)
             else:
                 self.gemm_nt(self.xn[i], lw["wqkv"], self.qkv[i])
                 N.rope_inplace(self.qkv[i], self.cos, self.sin, self.S, rot, hd)
             a = self._attention_fwd(i)
-            self.attn_flat = a
             self.gemm_nt(a, lw["wo"], self.ao)
             # h = x + attn_out ; hn = norm(h)
             N.rmsnorm_fwd(self.x[i], lw["wfn"], c.norm_eps, self.hn[i], self.rstd2[i], delta=self.ao, h_out=self.h[i])
-            if self.USE_TC:   # gate|up dual GEMM with the SwiGLU epilogue (K9 + K10)
+            if self.fused_gather is not None:
+                self.fused_gather.swiglu(i, self.hn[i], self.act[i], self.gate[i], self.up[i])
+            elif self.USE_TC:   # gate|up dual GEMM with the SwiGLU epilogue (K9 + K10)
                 N.gemm_swiglu(self.hn[i], lw["ww1"], lw["ww3"], self.act[i], self.gate[i], self.up[i])
             else:
                 self.gemm_nt(self.hn[i], lw["ww1"], self.gate[i])
                 self.gemm_nt(self.hn[i], lw["ww3"], self.up[i])
                 N.swiglu_fwd(self.gate[i], self.up[i], self.act[i])
             self.gemm_nt(self.act[i], lw["ww2"], self.ff)
-            # x_{i+1} = h + ff ; next norm (attention_norm of layer i+1, or the final norm)
-            if i + 1 < c.n_layers:
-                N.rmsnorm_fwd(self.h[i], self.lw[i + 1]["wan"], c.norm_eps, self.xn[i + 1], self.rstd1[i + 1],
-                              delta=self.ff, h_out=self.x[i + 1])
-            else:
-                N.rmsnorm_fwd(self.h[i], self.w_fn, c.norm_eps, self.xf, self.rstd_f, delta=self.ff,
-                              h_out=self.x[i + 1])
+        L = c.n_layers
+        self._need(L + 1)
+        # x_L = h_{L-1} + ff, fused with the final norm
+        N.rmsnorm_fwd(self.h[L - 1], self.w_fn, c.norm_eps, self.xf, self.rstd_f, delta=self.ff, h_out=self.x[L])
         self.gemm_nt(self.xf, self.w_out, self.logits)
         N.cross_entropy(self.logits, labels.view(-1), inv_n, self.row_loss, self.loss, write_grad=write_grad)
         return self.loss
@@ -325,6 +344,8 @@ class NativeEngine:
         rot = (H + KV) * hd
         L = c.n_layers
         dl = self.logits
+        if self.hook_params_bwd is not None:
+            self.hook_params_bwd(L + 1)
         self.gemm_tn(dl, self.xf, self.g_out)                     # dW_out
         self.gemm_nn(dl, self.w_out, self.dtmp)                   # d xf
         dx, spare = self.dx_a, self.dx_b
@@ -333,6 +354,8 @@ class NativeEngine:
             self.hook_grads(L + 1)
         for i in range(L - 1, -1, -1):
             lw = self.lw[i]
+            if self.hook_params_bwd is not None:
+                self.hook_params_bwd(i + 1)
             # x_{i+1} = h + w2(act)
             self.gemm_tn(dx, self.act[i], lw["gw2"])
             self.gemm_nn(dx, lw["ww2"], self.dact)
@@ -510,20 +533,32 @@ class NativeTrainer:
         """Flat ranges of exp_avg / exp_avg_sq this rank maintains."""
         return [(0, self.flat.numel)]
 
+    def checkpoint_segments(self):
+        """(buffer, flat_lo, flat_hi, device tensor) pieces this rank writes into its shard file."""
+        f, out = self.flat, []
+        for lo, hi in self._moment_ranges():
+            out += [("p", lo, hi, f.p[lo:hi]), ("m", lo, hi, f.m[lo:hi]), ("v", lo, hi, f.v[lo:hi])]
+        return out
+
+    def restore_targets(self, n_valid: int):
+        """(buffer, flat_lo, flat_hi, device tensor) pieces this rank needs back from a checkpoint."""
+        f = self.flat
+        out = [("p", 0, n_valid, f.p[:n_valid])]
+        for lo, hi in self._moment_ranges():
+            hi = min(hi, n_valid)
+            if lo < hi:
+                out += [("m", lo, hi, f.m[lo:hi]), ("v", lo, hi, f.v[lo:hi])]
+        return out
+
     def _load_sharded(self, ckpt: dict) -> None:
         """Shard files -> device, straight through the native reader (no CPU state_dict is ever built)."""
         from ..ckpt.sharded import read_range_to_device
         d, m, f = ckpt["_sharded_dir"], ckpt["_manifest"], self.flat
         if [list(x[1]) for x in m["layout"]] != [list(s) for _, s, _, _ in f.layout]:
             raise ValueError("checkpoint was written for a different model shape")
-        n_ck = m["flat_numel"]   # padding at the tail may differ with the world size; the payload does not
-        n = min(n_ck, f.numel)
-        read_range_to_device(d, m, "p", 0, n, f.p[:n])
-        for lo, hi in self._moment_ranges():
-            hi = min(hi, n)
-            if lo < hi:
-                read_range_to_device(d, m, "m", lo, hi, f.m[lo:hi])
-                read_range_to_device(d, m, "v", lo, hi, f.v[lo:hi])
+        n = min(m["flat_numel"], f.numel)   # padding at the tail may differ with the world size; the payload does not
+        for buf, lo, hi, dst in self.restore_targets(n):
+            read_range_to_device(d, m, buf, lo, hi, dst)
         g = m["optimizer"]["param_groups"][0]
         for k, v in g.items():
             self.optimizer.param_groups[0][k] = tuple(v) if k == "betas" else v

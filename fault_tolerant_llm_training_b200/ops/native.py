@@ -78,6 +78,10 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_ckpt_write", [ctypes.c_char_p, I, P, P, P, I, I, P])
     _sig(L, "ftl_ckpt_read", [ctypes.c_char_p, I, P, P, P, I, P])
     _sig(L, "ftl_ckpt_last_error", [], ctypes.c_char_p)
+    _sig(L, "ftl_gemm_qkv_rope_gather", [P, I64, P, I64, P, I64, P, P, I, I, I, I, I, I, P, I64, I, I, I, P, P])
+    _sig(L, "ftl_gemm_swiglu_gather", [P, I64, P, P, I64, P, P, P, I64, I, I, I, P, I64, I64, I, I, I, P, P])
+    _sig(L, "ftl_fsdp_gather", [P, I64, P, I64, I, I, P, I, P])
+    _sig(L, "ftl_adamw_shard", [P, P, P, P, I64, P, P, P, P, I, P])
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -340,3 +344,43 @@ def ckpt_read(path: str, segments, nthreads: int = 4) -> dict:
     if code != 0:
         raise NativeError(f"ftl_ckpt_read({path}) failed: {lib().ftl_ckpt_last_error().decode()}")
     return {"total_s": t[3]}
+
+
+# ---- fully-sharded path (csrc/gemm_tc.cu gather variants, csrc/comm.cu) -----------------------------------
+def gemm_qkv_rope_gather(x, wqkv, qkv, cos, sin, seq_len, head_dim, rot_cols, peer_shards, shard_off, rows_per_rank,
+                         rank, world, scratch):
+    """QKV projection + RoPE whose weight operand is all-gathered from the ranks' shards inside the kernel.
+    wqkv is the local [N, K] staging matrix the kernel fills while it computes."""
+    _mat(x), _mat(wqkv), _mat(qkv)
+    M, K = x.shape
+    Nq = wqkv.shape[0]
+    assert wqkv.is_contiguous() and scratch.dtype == torch.int32 and scratch.numel() >= 1 + Nq // 128
+    _check(lib().ftl_gemm_qkv_rope_gather(_ptr(x), x.stride(0), _ptr(wqkv), wqkv.stride(0), _ptr(qkv), qkv.stride(0),
+                                          _ptr(cos), _ptr(sin), M, Nq, K, seq_len, head_dim, rot_cols, _ptr(peer_shards),
+                                          shard_off, rows_per_rank, rank, world, _ptr(scratch), _stream()),
+           "ftl_gemm_qkv_rope_gather")
+    return qkv
+
+
+def gemm_swiglu_gather(x, w1, w3, act, gate, up, peer_shards, off_w1, off_w3, rows_per_rank, rank, world, scratch):
+    _mat(x), _mat(w1), _mat(w3), _mat(act)
+    M, K = x.shape
+    H = w1.shape[0]
+    assert w1.is_contiguous() and w3.is_contiguous() and scratch.numel() >= 1 + 2 * (H // 128)
+    _check(lib().ftl_gemm_swiglu_gather(_ptr(x), x.stride(0), _ptr(w1), _ptr(w3), w1.stride(0), _ptr(act), _ptr(gate),
+                                        _ptr(up), act.stride(0), M, H, K, _ptr(peer_shards), off_w1, off_w3, rows_per_rank,
+                                        rank, world, _ptr(scratch), _stream()), "ftl_gemm_swiglu_gather")
+    return act
+
+
+def fsdp_gather(peer_shards, shard_off, dst, n_per_rank, rank, world, status, max_ctas=0):
+    """dst[r * n : (r + 1) * n] = rank r's shard, for every r (plain parameter all-gather)."""
+    _bf16(dst)
+    _check(lib().ftl_fsdp_gather(_ptr(peer_shards), shard_off, _ptr(dst), n_per_rank, rank, world, _ptr(status), max_ctas,
+                                 _stream()), "ftl_fsdp_gather")
+
+
+def adamw_shard(p, g, m, v, hyper, stats, status, commits=None, max_ctas=0):
+    _bf16(p, g, m, v)
+    _check(lib().ftl_adamw_shard(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), _ptr(hyper), _ptr(stats), _ptr(status),
+                                 _ptr(commits), max_ctas, _stream()), "ftl_adamw_shard")

@@ -1,0 +1,325 @@
+"""Fully-sharded engine (ZeRO-3 style): BASELINE.json fused path 2 — the parameter all-gather is pulled into
+the QKV and gate/up GEMMs that consume the gathered weights.
+
+Persistent state per rank is only ITS row shard of every weight matrix (one compact peer-mapped buffer),
+the matching AdamW moments, and the local gradient buffer.  Full weights exist two buckets at a time, in two
+staging slots (bucket = embedding | layer i | final norm + head):
+
+  forward, layer i   wo, w2 and the norm weights of the layer are gathered by the plain all-gather kernel on the
+                     comm stream while the previous layer computes;  wq|wk|wv and w1, w3 — 80 % of the layer's
+                     bytes — are NOT gathered ahead: `ftl_gemm_qkv_rope_gather` / `ftl_gemm_swiglu_gather`
+                     pull the owners' rows over NVLink from inside the GEMM (the epilogue warps of every CTA
+                     move 16-row slices while they wait for accumulators; the TMA producers wait per 128-row
+                     half block), so the transfer overlaps the MMAs tile by tile
+  backward, layer i  the whole bucket is re-gathered (plain kernel, one bucket ahead of the backward GEMMs)
+  update             gradient reduce-scatter ⊕ norm² per shard under backward, then clip ⊕ AdamW on the compact
+                     shards; no parameter all-gather follows — the next forward reads the shards directly
+
+The schedule, barriers, abort/commit logic and the sharded checkpoint writer are those of the pipelined
+data-parallel engine (parallel/pipeline.py); only the ownership map and the parameter path differ.
+The reference has no counterpart.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Tuple
+
+import torch
+
+from ..models.engine import FlatState
+from ..ops import native as N
+from .pipeline import PipelinedTrainer
+from .symm import SymmetricBuffers
+
+
+class _Unit:
+    """One row-sharded matrix: flat range [off, off + numel), rows x cols, `shard` elements per rank."""
+    __slots__ = ("name", "off", "numel", "rows", "cols", "shard", "coff", "bucket", "fused")
+
+    def __init__(self, name, off, numel, rows, cols, shard, coff, bucket, fused):
+        self.name, self.off, self.numel, self.rows, self.cols = name, off, numel, rows, cols
+        self.shard, self.coff, self.bucket, self.fused = shard, coff, bucket, fused
+
+
+class FsdpState(FlatState):
+    """Flat gradient buffer as usual; parameters are views into the two staging slots (by bucket parity)."""
+
+    def bind_slots(self, slots: List[torch.Tensor], bucket_of: Dict[str, int], bucket_lo: List[int]) -> None:
+        self._slots, self._bucket_of, self._bucket_lo = slots, bucket_of, bucket_lo
+
+    def param_view(self, name: str) -> torch.Tensor:
+        off, n, shape = self.index[name]
+        b = self._bucket_of[name]
+        rel = off - self._bucket_lo[b]
+        return self._slots[b % 2][rel:rel + n].view(shape)
+
+    def param_span(self, first: str, last: str, shape) -> torch.Tensor:
+        o0, _, _ = self.index[first]
+        o1, n1, _ = self.index[last]
+        b = self._bucket_of[first]
+        rel = o0 - self._bucket_lo[b]
+        return self._slots[b % 2][rel:rel + (o1 + n1 - o0)].view(shape)
+
+
+class FsdpTrainer(PipelinedTrainer):
+    GATHER_CTAS = 64
+
+    # ---- state ---------------------------------------------------------------------------------------------------
+    def _make_flat_state(self) -> FlatState:
+        env, W, L = self.env, self.env.world_size, self.cfg.n_layers
+        from ..models.llama import flat_size, param_layout
+        layout = param_layout(self.model)
+        numel = (flat_size(layout) + 1023) // 1024 * 1024
+        index = {name: (off, n, shape) for name, shape, off, n in layout}
+        # ---- buckets (forward order) and shard units
+        starts = [index["tok_embeddings.weight"][0]] + [index[f"layers.{i}.attention.wq.weight"][0] for i in range(L)]
+        starts += [index["norm.weight"][0], numel]
+        self.buckets = [(starts[i], starts[i + 1]) for i in range(L + 2)]
+        d = self.cfg.dim
+        self.units: List[_Unit] = []
+        self.bucket_units: List[List[_Unit]] = [[] for _ in range(L + 2)]
+        coff = 0
+
+        def add(name, off, rows, cols, bucket, fused=False):
+            nonlocal coff
+            n = rows * cols
+            if n % (W * 8):
+                raise ValueError(f"{name}: {n} elements do not split into {W} 16-byte-aligned shards")
+            u = _Unit(name, off, n, rows, cols, n // W, coff, bucket, fused)
+            coff += (u.shard + 127) // 128 * 128
+            self.units.append(u)
+            self.bucket_units[bucket].append(u)
+            return u
+
+        def mat(name, bucket, fused=False):
+            off, n, shape = index[name]
+            return add(name, off, shape[0] if len(shape) == 2 else 1, shape[1] if len(shape) == 2 else shape[0], bucket, fused)
+
+        mat("tok_embeddings.weight", 0)
+        self.layer_units = []
+        for i in range(L):
+            b, pre = i + 1, f"layers.{i}."
+            oq = index[pre + "attention.wq.weight"][0]
+            ov, nv, _ = index[pre + "attention.wv.weight"]
+            qkv_rows = (ov + nv - oq) // d
+            fusable = (qkv_rows // W) % 128 == 0 and (self.cfg.ffn_hidden // W) % 128 == 0 and W > 0
+            lu = {"qkv": add(pre + "attention.wqkv", oq, qkv_rows, d, b, fused=fusable),
+                  "wo": mat(pre + "attention.wo.weight", b),
+                  "w1": mat(pre + "feed_forward.w1.weight", b, fused=fusable),
+                  "w2": mat(pre + "feed_forward.w2.weight", b),
+                  "w3": mat(pre + "feed_forward.w3.weight", b, fused=fusable),
+                  "an": mat(pre + "attention_norm.weight", b), "fn": mat(pre + "ffn_norm.weight", b)}
+            self.layer_units.append(lu)
+        mat("norm.weight", L + 1)
+        mat("output.weight", L + 1)
+        self.own_numel = (coff + 1023) // 1024 * 1024
+        max_bucket = max(hi - lo for lo, hi in self.buckets)
+        flag_words = N.lib().ftl_comm_flag_words()
+        self.symm = SymmetricBuffers(env, {"own": self.own_numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64})
+        self.p_own = self.symm.tensor("own", torch.bfloat16)
+        self.m_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
+        self.v_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
+        self.stage = [torch.zeros(max_bucket, dtype=torch.bfloat16, device=self.device) for _ in range(2)]
+        # ---- move the freshly initialised parameters into the shards, then drop the full copies
+        with torch.no_grad():
+            params = dict(self.model.named_parameters())
+            full = {}
+            for u in self.units:
+                if u.name.endswith("attention.wqkv"):
+                    pre = u.name[:-len("wqkv")]
+                    src = torch.cat([params[pre + k + ".weight"].reshape(-1) for k in ("wq", "wk", "wv")])
+                else:
+                    src = params[u.name].reshape(-1)
+                self.p_own[u.coff:u.coff + u.shard].copy_(src[env.rank * u.shard:(env.rank + 1) * u.shard])
+            del full
+        bufs = {"p": lambda n: torch.zeros(0, dtype=torch.bfloat16, device=self.device),   # no full parameter buffer
+                "g": lambda n: self.symm.tensor("g", torch.bfloat16),
+                "m": lambda n: torch.zeros(0, dtype=torch.bfloat16, device=self.device),
+                "v": lambda n: torch.zeros(0, dtype=torch.bfloat16, device=self.device)}
+        flat = FsdpState.__new__(FsdpState)
+        flat.layout, flat.numel = layout, numel
+        flat.p, flat.g, flat.m, flat.v = bufs["p"](0), bufs["g"](numel), bufs["m"](0), bufs["v"](0)
+        flat.index = index
+        bucket_of = {}
+        for name, (off, n, shape) in index.items():
+            bucket_of[name] = max(b for b, (lo, hi) in enumerate(self.buckets) if lo <= off)
+        flat.bind_slots(self.stage, bucket_of, [lo for lo, _ in self.buckets])
+        with torch.no_grad():
+            for name, prm in self.model.named_parameters():
+                off, n, shape = index[name]
+                prm.data = torch.empty(0, dtype=torch.bfloat16, device=self.device)   # full weights are never resident
+                prm.grad = None
+        self._finish_pipeline_state(flat)
+        # ---- staging-slot bookkeeping
+        NB = L + 2
+        self.resident = [-1, -1]            # bucket currently in each slot
+        self.resident_full = [False, False]  # ... including the matrices the fused GEMMs gather themselves
+        self.ev_gather = [torch.cuda.Event() for _ in range(NB)]
+        self.ev_slot_free = [torch.cuda.Event(), torch.cuda.Event()]
+        self.gather_scratch = torch.zeros(1 + 2 * (self.cfg.ffn_hidden // 128 + self.cfg.qkv_dim // 128 + 2),
+                                          dtype=torch.int32, device=self.device)
+        return flat
+
+    def _finish_pipeline_state(self, flat: FlatState) -> None:
+        """The part of PipelinedTrainer._make_flat_state that does not allocate parameter buffers."""
+        import os
+        self.ranges = self._owned_ranges(flat)
+        NB = len(self.buckets)
+        self.parts = N.dp_partials(self.RS_CTAS)
+        self.range_slot, k = [], 0
+        for rs in self.ranges:
+            self.range_slot.append(list(range(k, k + len(rs))))
+            k += len(rs)
+        self.rs_partials = torch.zeros(max(k, 1) * self.parts, dtype=torch.float32, device=self.device)
+        self.comm_status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.commits = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.slots = self.symm.tensor("slots", torch.float32)
+        self.epoch = 0
+        self.barrier_timeout_ms = int(os.environ.get("FTL_BARRIER_TIMEOUT_MS", "120000"))
+        self.comm = torch.cuda.Stream(device=self.device, priority=-1)
+        self.ev_grad = [torch.cuda.Event() for _ in range(NB)]
+        self.ev_param = [torch.cuda.Event() for _ in range(NB)]
+        self.ev_step = torch.cuda.Event()
+        self._params_pending = False
+        self._hyper = None
+
+    def _owned_ranges(self, flat) -> List[List[Tuple[int, int]]]:
+        r = self.env.rank
+        return [[(u.off + r * u.shard, u.off + (r + 1) * u.shard) for u in us] for us in self.bucket_units]
+
+    # ---- parameter path: gathers --------------------------------------------------------------------------------
+    def _gather(self, b: int, include_fused: bool) -> None:
+        """Enqueue (comm stream) the plain all-gather of bucket b into staging slot b % 2, unless it is there already.
+        The caller guarantees that every kernel reading the slot's previous occupant has been enqueued on the main
+        stream: an event recorded there now is what the gather waits for."""
+        k = b % 2
+        have = self.resident[k] == b
+        if have and (self.resident_full[k] or not include_fused):
+            return
+        env, lo = self.env, self.buckets[b][0]
+        if not have:
+            self.ev_slot_free[k].record()                      # main stream: previous occupant no longer needed
+        with torch.cuda.stream(self.comm):
+            if not have:
+                self.comm.wait_event(self.ev_slot_free[k])
+            for u in self.bucket_units[b]:
+                if (u.fused and not include_fused) or (have and not u.fused):
+                    continue
+                N.fsdp_gather(self.symm.table("own"), u.coff, self.stage[k][u.off - lo:u.off - lo + u.numel], u.shard,
+                              env.rank, env.world_size, self.comm_status, max_ctas=self.GATHER_CTAS)
+            self.ev_gather[b].record()
+        self.resident[k] = b
+        self.resident_full[k] = include_fused or not any(u.fused for u in self.bucket_units[b])
+
+    def _wait_params(self, b: int) -> None:
+        """Forward: the engine is about to read bucket b (all kernels of buckets < b are already enqueued)."""
+        main = torch.cuda.current_stream()
+        fused = self.engine is not None and self.engine.fused_gather is not None
+        self._gather(b, include_fused=not fused)      # no-op when the prefetch below already issued it
+        main.wait_event(self.ev_gather[b])
+        if self._params_pending:
+            main.wait_event(self.ev_param[b])         # the fused GEMMs read bucket b's shards on the peers directly
+        if b + 1 < len(self.buckets):
+            self._gather(b + 1, include_fused=not fused)   # prefetch into the other slot while bucket b computes
+
+    def _params_for_backward(self, b: int) -> None:
+        """Backward: the engine is about to read bucket b (all kernels of buckets > b are already enqueued)."""
+        main = torch.cuda.current_stream()
+        self._gather(b, include_fused=True)
+        main.wait_event(self.ev_gather[b])
+        if b - 1 >= 1:
+            self._gather(b - 1, include_fused=True)   # prefetch the next (lower) layer
+
+    def _ensure_engine(self, B: int, S: int) -> None:
+        fresh = self.engine is None or (self.engine.B, self.engine.S) != (B, S)
+        super()._ensure_engine(B, S)
+        if fresh:
+            self.engine.hook_params_bwd = self._params_for_backward
+            if all(lu["qkv"].fused for lu in self.layer_units) and self.engine.USE_TC and N.has("ftl_gemm_qkv_rope_gather"):
+                self.engine.fused_gather = self
+
+    # gather-fused GEMMs, called by the engine in the forward of layer i (main stream)
+    def qkv(self, i: int, x: torch.Tensor, out: torch.Tensor) -> None:
+        c, u, e = self.cfg, self.layer_units[i]["qkv"], self.engine
+        N.gemm_qkv_rope_gather(x, e.lw[i]["wqkv"], out, e.cos, e.sin, e.S, c.head_dim, (c.n_heads + c.n_kv_heads) * c.head_dim,
+                               self.symm.table("own"), u.coff, u.rows // self.env.world_size, self.env.rank,
+                               self.env.world_size, self.gather_scratch)
+
+    def swiglu(self, i: int, x: torch.Tensor, act: torch.Tensor, gate: torch.Tensor, up: torch.Tensor) -> None:
+        lu, e = self.layer_units[i], self.engine
+        N.gemm_swiglu_gather(x, e.lw[i]["ww1"], e.lw[i]["ww3"], act, gate, up, self.symm.table("own"), lu["w1"].coff,
+                             lu["w3"].coff, lu["w1"].rows // self.env.world_size, self.env.rank, self.env.world_size,
+                             self.gather_scratch)
+        self.resident_full[(i + 1) % 2] = True        # wq|wk|wv, w1, w3 of this layer are now in the slot too
+
+    # ---- update: AdamW on the compact shards, no all-gather -----------------------------------------------------
+    def _update_bucket(self, b: int, hyper: torch.Tensor) -> None:
+        r = self.env.rank
+        for u in self.bucket_units[b]:
+            lo = u.off + r * u.shard
+            N.adamw_shard(self.p_own[u.coff:u.coff + u.shard], self.flat.g[lo:lo + u.shard],
+                          self.m_own[u.coff:u.coff + u.shard], self.v_own[u.coff:u.coff + u.shard], hyper, self.stats,
+                          self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
+
+    def _after_update(self, b: int) -> None:
+        k = b % 2
+        if self.resident[k] == b:
+            self.resident[k] = -1                      # the staged copy of bucket b is stale now
+
+    def step(self, inputs, labels):
+        out = super().step(inputs, labels)
+        return out
+
+    # ---- checkpoints: compact shards with their flat ranges ------------------------------------------------------
+    def checkpoint_segments(self):
+        r, out = self.env.rank, []
+        for u in self.units:
+            lo, hi = u.off + r * u.shard, u.off + (r + 1) * u.shard
+            sl = slice(u.coff, u.coff + u.shard)
+            out += [("p", lo, hi, self.p_own[sl]), ("m", lo, hi, self.m_own[sl]), ("v", lo, hi, self.v_own[sl])]
+        return out
+
+    def restore_targets(self, n_valid: int):
+        return self.checkpoint_segments()
+
+    def load_state(self, ckpt: dict) -> None:
+        if "_sharded_dir" not in ckpt:
+            # reference-layout file: scatter the full tensors into the shards
+            r = self.env.rank
+            sd, st = ckpt["model"], ckpt["optimizer"]["state"]
+            names = [n for n, _, _, _ in self.flat.layout]
+            full = {"p": {}, "m": {}, "v": {}}
+            for i, n in enumerate(names):
+                full["p"][n] = sd[n]
+                full["m"][n], full["v"][n] = st[i]["exp_avg"], st[i]["exp_avg_sq"]
+            for u in self.units:
+                for key, dst in (("p", self.p_own), ("m", self.m_own), ("v", self.v_own)):
+                    if u.name.endswith("attention.wqkv"):
+                        pre = u.name[:-len("wqkv")]
+                        src = torch.cat([full[key][pre + k + ".weight"].reshape(-1) for k in ("wq", "wk", "wv")])
+                    else:
+                        src = full[key][u.name].reshape(-1)
+                    dst[u.coff:u.coff + u.shard].copy_(src[r * u.shard:(r + 1) * u.shard])
+            g = ckpt["optimizer"]["param_groups"][0]
+            for k, v in g.items():
+                if k != "params":
+                    self.optimizer.param_groups[0][k] = v
+            self.optimizer.steps_done = int(float(next(iter(st.values()))["step"])) if st else 0
+            self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
+            torch.cuda.synchronize()
+            self.env.barrier()
+        else:
+            super().load_state(ckpt)
+        self.resident = [-1, -1]
+
+    def full_parameters(self) -> Dict[str, torch.Tensor]:
+        """All-gather every parameter (testing / export); not used on the training path."""
+        torch.cuda.synchronize()
+        self.env.barrier()
+        out = {}
+        for u in self.units:
+            buf = torch.empty(u.numel, dtype=torch.bfloat16, device=self.device)
+            N.fsdp_gather(self.symm.table("own"), u.coff, buf, u.shard, self.env.rank, self.env.world_size, self.comm_status)
+            out[u.name] = buf.view(u.rows, u.cols) if u.rows > 1 else buf
+        torch.cuda.synchronize()
+        self.env.barrier()
+        return out

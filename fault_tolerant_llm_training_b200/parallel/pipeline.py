@@ -51,14 +51,14 @@ class PipelinedTrainer(NativeTrainer):
         starts += [flat.index[f"layers.{i}.attention.wq.weight"][0] for i in range(L)]
         starts += [flat.index["norm.weight"][0], numel]
         self.buckets: List[Tuple[int, int]] = [(starts[i], starts[i + 1]) for i in range(L + 2)]
-        self.sub: List[Tuple[int, int]] = []          # this rank's sub-shard of each bucket
-        for lo, hi in self.buckets:
-            sz = ((hi - lo + W - 1) // W + 7) // 8 * 8
-            a = min(lo + env.rank * sz, hi)
-            self.sub.append((a, min(a + sz, hi)))
+        self.ranges = self._owned_ranges(flat)        # per bucket: flat ranges (lo, hi) this rank reduces and updates
         NB = len(self.buckets)
         self.parts = N.dp_partials(self.RS_CTAS)
-        self.rs_partials = torch.zeros(NB * self.parts, dtype=torch.float32, device=self.device)
+        self.range_slot, k = [], 0                    # index of each range's partial-sum slice
+        for rs in self.ranges:
+            self.range_slot.append(list(range(k, k + len(rs))))
+            k += len(rs)
+        self.rs_partials = torch.zeros(max(k, 1) * self.parts, dtype=torch.float32, device=self.device)
         self.comm_status = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.commits = torch.zeros(1, dtype=torch.int64, device=self.device)
         self.slots = self.symm.tensor("slots", torch.float32)
@@ -73,8 +73,18 @@ class PipelinedTrainer(NativeTrainer):
         self._hyper = None
         return flat
 
+    def _owned_ranges(self, flat: FlatState) -> List[List[Tuple[int, int]]]:
+        """Data parallel: every bucket is cut into W equal contiguous sub-shards; rank r owns the r-th."""
+        W, r, out = self.env.world_size, self.env.rank, []
+        for lo, hi in self.buckets:
+            sz = ((hi - lo + W - 1) // W + 7) // 8 * 8
+            a = min(lo + r * sz, hi)
+            e = min(a + sz, hi)
+            out.append([(a, e)] if e > a else [])
+        return out
+
     def _moment_ranges(self):
-        return [(a, b) for a, b in self.sub if b > a]
+        return [rg for rs in self.ranges for rg in rs]
 
     # ---- hooks called from the engine ----------------------------------------------------------------------------
     def _ensure_engine(self, B: int, S: int) -> None:
@@ -98,16 +108,13 @@ class PipelinedTrainer(NativeTrainer):
     def _grads_done(self, b: int) -> None:
         """Backward finished writing bucket b's gradients: reduce this rank's sub-shard on the comm stream."""
         self.ev_grad[b].record()
-        a, e = self.sub[b]
         with torch.cuda.stream(self.comm):
             self.comm.wait_event(self.ev_grad[b])
             self._barrier()          # every rank's bucket-b gradients are complete
-            part = self.rs_partials[b * self.parts:(b + 1) * self.parts]
-            if e > a:
+            for (a, e), k in zip(self.ranges[b], self.range_slot[b]):
+                part = self.rs_partials[k * self.parts:(k + 1) * self.parts]
                 N.dp_reduce_scatter(self.symm.table("g"), self.env.rank, self.env.world_size, a, e - a, part,
                                     self.comm_status, max_ctas=self.RS_CTAS)
-            else:
-                part.zero_()
 
     # ---- step pieces ---------------------------------------------------------------------------------------------
     def _begin_step(self, hyper: torch.Tensor) -> None:
@@ -123,15 +130,24 @@ class PipelinedTrainer(NativeTrainer):
             self._barrier()          # all slots written; nobody still reads my gradients for phase 1
             N.dp_finalize(self.slots, W, hyper, self.stats, loss, clip=(self.clip_mode == "clip"))
             self._result_handle = self._publish_result_on_comm(loss)
-            for b, (a, e) in enumerate(self.sub):
-                if e > a:
-                    N.dp_adamw_allgather(self.symm.table("p"), f.g, f.m, f.v, env.rank, W, a, e - a, hyper, self.stats,
-                                         self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
+            for b in range(len(self.buckets)):
+                self._update_bucket(b, hyper)
                 self._barrier()      # bucket b is updated on every rank
                 self.ev_param[b].record()
+                self._after_update(b)
         self._params_pending = True
         self.optimizer.steps_done += 1
         self.optimizer._opt_called = True   # the update ran inside the fused kernels
+
+    def _update_bucket(self, b: int, hyper: torch.Tensor) -> None:
+        """clip ⊕ AdamW ⊕ all-gather of this rank's ranges of bucket b (runs on the comm stream)."""
+        f, env = self.flat, self.env
+        for a, e in self.ranges[b]:
+            N.dp_adamw_allgather(self.symm.table("p"), f.g, f.m, f.v, env.rank, env.world_size, a, e - a, hyper,
+                                 self.stats, self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
+
+    def _after_update(self, b: int) -> None:
+        pass
 
     def _publish_result_on_comm(self, loss: torch.Tensor) -> LossHandle:
         slot = self._result_slot
@@ -153,7 +169,7 @@ class PipelinedTrainer(NativeTrainer):
     def committed_updates(self) -> int:
         """Number of optimizer steps fully applied on the device (each applies one update per non-empty bucket)."""
         torch.cuda.synchronize()
-        per_step = sum(1 for a, e in self.sub if e > a)
+        per_step = sum(len(rs) for rs in self.ranges)
         return int(self.commits.item()) // max(per_step, 1)
 
     def abort_peers(self) -> None:

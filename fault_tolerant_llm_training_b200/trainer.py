@@ -109,7 +109,9 @@ def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: floa
         if env.distributed and parallel == "none":
             raise ValueError("--parallel none with WORLD_SIZE > 1: ranks would train unsynchronised copies")
         import os
-        if os.environ.get("FTL_PIPELINE", "1") != "0":
+        if parallel == "fsdp":
+            from .parallel.fsdp import FsdpTrainer as NativeTrainer  # noqa: F811
+        elif os.environ.get("FTL_PIPELINE", "1") != "0":
             # default: bucketed, overlapped reduce-scatter / AdamW / all-gather on a second stream (1..8 GPUs)
             from .parallel.pipeline import PipelinedTrainer as NativeTrainer  # noqa: F811
         elif env.distributed:
