@@ -248,3 +248,39 @@ class BatchStream:
             for _ in range(batches):
                 self._make(0)
         self.batches_consumed = batches
+
+
+def _smoke(argv=None) -> None:
+    """Dataset smoke run (reference: `python dataset.py`, dataset.py:104-166): builds both datasets, prints the
+    batch shapes and the share of label positions masked out of the loss.  Works offline: without --dataset a
+    synthetic parquet is written, without a reachable HF tokenizer the offline tokenizer is used."""
+    import argparse
+    import os
+    import tempfile
+
+    from .synthetic import write_synthetic_parquet
+    from .tokenizer import load_tokenizer
+
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--dataset", default="")
+    ap.add_argument("--tokenizer-name-or-path", default="offline")
+    ap.add_argument("--sequence-length", type=int, default=4096)
+    ap.add_argument("--batch-size", type=int, default=32)
+    a = ap.parse_args(argv)
+    tok = load_tokenizer(a.tokenizer_name_or_path)
+    path = a.dataset or write_synthetic_parquet(os.path.join(tempfile.mkdtemp(), "smoke.parquet"), num_docs=64,
+                                                max_len=2 * a.sequence_length, vocab_size=tok.vocab_size)
+    ds = ParquetDataset(path, tok, a.sequence_length, training_samples=a.batch_size)
+    print("Decoded sample:", tok.decode(ds[0]["input_ids"][:20]))
+    padded = BatchStream(ds, a.batch_size, CollatorForCLM(a.sequence_length, tok.pad_token_id), prefetch=0)
+    packed = BatchStream(IterableParquetDataset(path, tok, a.sequence_length, bos_token_id=tok.bos_token_id or 1),
+                         a.batch_size)
+    for name, stream in (("ParquetDataset + CollatorForCLM", padded), ("IterableParquetDataset", packed)):
+        x, y = next(stream)
+        ignored = int((y == -100).sum())
+        print(f"{name}: input {tuple(x.shape)} labels {tuple(y.shape)} | ignored tokens in loss: {ignored} of {y.numel()} "
+              f"({ignored / y.numel() * 100:.2f}%)")
+
+
+if __name__ == "__main__":
+    _smoke()

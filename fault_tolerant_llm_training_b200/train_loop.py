@@ -87,7 +87,10 @@ def train(args) -> None:
                            clip_mode=args.clip_mode, seed=args.seed, parallel=args.parallel,
                            fused_optimizer=args.fused_optimizer, bucket_mb=args.bucket_mb,
                            cuda_graph=args.cuda_graph, keep_shards=args.sharded_checkpoint,
-                           consolidate=not args.no_consolidate)
+                           consolidate=not args.no_consolidate, compile_model=args.compile)
+    if args.compile:
+        logger.info("Using `torch.compile`" if env.device.type != "cuda" else
+                    "`--compile` ignored: the B200 engine runs hand-written kernels, not a traced graph")
     if checkpoint is not None:
         trainer.load_state(checkpoint)
         logger.info("Model loaded from checkpoint")

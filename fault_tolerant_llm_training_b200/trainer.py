@@ -30,11 +30,16 @@ from .parallel.env import DistEnv
 
 class TorchTrainer:
     def __init__(self, cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
-                 grad_max_norm: float, clip_mode: str = "clip", seed: int = 0, fused_optimizer: bool = False):
+                 grad_max_norm: float, clip_mode: str = "clip", seed: int = 0, fused_optimizer: bool = False,
+                 compile_model: bool = False):
         self.cfg, self.env = cfg, env
         self.device = env.device
         self.model = build_model(cfg, dtype, self.device, seed=seed)
         self.model.train()
+        # reference: `--compile` -> torch.compile(model, fullgraph=True) (train.py:61-63).  Honoured on this portable
+        # path only (the B200 engine has no tracing compiler on its hot path).  The compiled callable is kept apart
+        # from `self.model`, so checkpoints keep un-prefixed names and resume stays strict.
+        self._forward = torch.compile(self.model, fullgraph=True) if compile_model else self.model
         # torch.optim.AdamW with library defaults: betas (0.9, 0.999), eps 1e-8, weight_decay 0.01 on
         # every parameter, as the reference (train.py:68)
         self.optimizer = torch.optim.AdamW(self.model.parameters(), lr=lr,
@@ -51,7 +56,7 @@ class TorchTrainer:
         inputs = inputs.to(self.device, non_blocking=True)
         labels = labels.to(self.device, non_blocking=True)
         self.optimizer.zero_grad()
-        logits = self.model(inputs)
+        logits = self._forward(inputs)
         loss = T.cross_entropy_sum(logits, labels) / max(n_items, 1)
         del logits
         loss.backward()
@@ -99,7 +104,8 @@ class TorchTrainer:
 def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
                  grad_max_norm: float = 1.0, clip_mode: str = "clip", seed: int = 0, parallel: str = "auto",
                  fused_optimizer: bool = False, bucket_mb: int = 512, cuda_graph: bool = False,
-                 force_torch: bool = False, keep_shards: bool = False, consolidate: bool = True):
+                 force_torch: bool = False, keep_shards: bool = False, consolidate: bool = True,
+                 compile_model: bool = False):
     """Factory used by train.py, bench.py and the tests."""
     if parallel == "auto":
         parallel = "dp" if env.distributed else "none"
@@ -122,4 +128,4 @@ def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: floa
                              parallel=parallel, bucket_mb=bucket_mb, cuda_graph=cuda_graph,
                              keep_shards=keep_shards, consolidate=consolidate)
     return TorchTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps, grad_max_norm=grad_max_norm,
-                        clip_mode=clip_mode, seed=seed, fused_optimizer=fused_optimizer)
+                        clip_mode=clip_mode, seed=seed, fused_optimizer=fused_optimizer, compile_model=compile_model)

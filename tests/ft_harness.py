@@ -51,11 +51,7 @@ class Job:
                 m = STEP_RE.search(line)
                 if m and signal_at is not None and not self.signalled and int(m.group(1)) >= signal_at:
                     self.signalled = True
-                    # like srun/torchrun forwarding: every process of the job step gets the signal
-                    try:
-                        os.killpg(self.proc.pid, sig)
-                    except ProcessLookupError:
-                        pass
+                    self._signal_job(sig)
 
         t = threading.Thread(target=pump, daemon=True)
         t.start()
@@ -66,6 +62,22 @@ class Job:
             self.returncode = -9
         t.join(timeout=10)
         self.text = "\n".join(self.lines)
+
+    def _signal_job(self, sig):
+        """Like srun's signal forwarding: every task of the job step gets the signal.  Under torchrun the workers
+        are signalled directly (the launcher itself neither handles nor forwards SIGUSR1)."""
+        import psutil
+        try:
+            kids = psutil.Process(self.proc.pid).children(recursive=True)
+        except psutil.NoSuchProcess:
+            kids = []
+        workers = [k for k in kids if any("train.py" in part for part in (k.cmdline() or []))]
+        targets = [k.pid for k in workers] if workers else [self.proc.pid]
+        for pid in targets:
+            try:
+                os.kill(pid, sig)
+            except ProcessLookupError:
+                pass
 
     @property
     def losses(self):
