@@ -454,7 +454,7 @@ class NativeTrainer:
         return self.env.sum_int(n_local)
 
     # -- one step (reference: train.py:93-110) ----------------------------------------------------
-    def step(self, inputs: torch.Tensor, labels: torch.Tensor) -> LossHandle:
+    def step(self, inputs: torch.Tensor, labels: torch.Tensor, n_items: Optional[int] = None) -> LossHandle:
         B, S = inputs.shape
         self._ensure_engine(B, S)
         launches0 = N.LAUNCHES
@@ -463,7 +463,8 @@ class NativeTrainer:
         # still checkpoints clean state (reference: get_total_norm(error_if_nonfinite=True), utils.py:61)
         while len(self._pending) >= 2:
             self._inspect(self._pending.pop(0))
-        n_items = self._global_token_count(int(labels.ne(-100).sum()))
+        if n_items is None:
+            n_items = self._global_token_count(int(labels.ne(-100).sum()))
         slot = self._slot
         self._slot = (slot + 1) % self.RING
         st = self._stage[slot]

@@ -68,6 +68,23 @@ class DistEnv:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.ctrl)
         return float(t.item())
 
+    def step_sync(self, stop_code: int, n_items: int):
+        """The ONE host collective of a training step: agree on a stop code and sum the token counts.
+
+        A single SUM all-reduce of [n_items, #timeout, #error, #cancel].  Because every step performs exactly this
+        collective and nothing else, a rank that fails locally can always pair with its peers' next step: it calls
+        step_sync(STOP_ERROR, 0) from its exception handler (train_loop).  Returns (agreed_code, total_items);
+        cancel beats error beats timeout, as in ft.signals."""
+        if not self.distributed:
+            return stop_code, n_items
+        t = torch.zeros(4, dtype=torch.int64)
+        t[0] = n_items
+        if 1 <= stop_code <= 3:
+            t[stop_code] = 1
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.ctrl)
+        code = 3 if t[3] > 0 else (2 if t[2] > 0 else (1 if t[1] > 0 else 0))
+        return code, int(t[0])
+
     def barrier(self) -> None:
         if self.distributed:
             dist.barrier(group=self.ctrl)

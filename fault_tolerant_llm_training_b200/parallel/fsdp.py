@@ -265,10 +265,6 @@ class FsdpTrainer(PipelinedTrainer):
         if self.resident[k] == b:
             self.resident[k] = -1                      # the staged copy of bucket b is stale now
 
-    def step(self, inputs, labels):
-        out = super().step(inputs, labels)
-        return out
-
     # ---- checkpoints: compact shards with their flat ranges ------------------------------------------------------
     def checkpoint_segments(self):
         r, out = self.env.rank, []

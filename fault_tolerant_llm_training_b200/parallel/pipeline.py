@@ -161,9 +161,9 @@ class PipelinedTrainer(NativeTrainer):
     def _publish_result(self, loss: torch.Tensor, slot: int) -> LossHandle:
         return self._result_handle      # recorded on the comm stream right after finalize
 
-    def step(self, inputs, labels):
+    def step(self, inputs, labels, n_items=None):
         self._result_slot = self._slot   # ring slot this step will use (base class advances _slot)
-        return super().step(inputs, labels)
+        return super().step(inputs, labels, n_items=n_items)
 
     # ---- fault tolerance -----------------------------------------------------------------------------------------
     def committed_updates(self) -> int:
@@ -173,7 +173,14 @@ class PipelinedTrainer(NativeTrainer):
         return int(self.commits.item()) // max(per_step, 1)
 
     def abort_peers(self) -> None:
+        """A rank that leaves the loop on its own first lets its already-enqueued steps finish (the peers still take
+        part in those), then raises the abort word so that peers' kernels waiting for a step this rank will never
+        run fall through their barriers with status 2 instead of spinning until the timeout."""
         if self.env.world_size > 1:
+            try:
+                torch.cuda.synchronize()
+            except RuntimeError:
+                pass
             N.raise_abort(self.symm.table("flags"), self.env.world_size)
             torch.cuda.synchronize()
 

@@ -29,7 +29,7 @@ from .data.datasets import BatchStream, CollatorForCLM, IterableParquetDataset, 
 from .data.synthetic import write_synthetic_parquet
 from .data.tokenizer import load_tokenizer
 from .ft.exit_handler import handle_exit
-from .ft.signals import (STOP_NONE, SignalFlags, TrainingInterrupt, error_type_of,
+from .ft.signals import (STOP_ERROR, STOP_NONE, SignalFlags, TrainingInterrupt, error_type_of,
                          stop_code_to_error_type)
 from .log import logger
 from .parallel.env import init_dist
@@ -110,23 +110,31 @@ def train(args) -> None:
     t_window, window_steps = time.perf_counter(), 0
     exit_kw = dict(rank=env.rank, world_size=env.world_size, resubmit_cmd=args.resubmit_cmd,
                    resume_id=args.checkpoint_id, flags=flags)
+    # FTL_INJECT_RANK_ERROR="rank:step" raises on one rank only (test hook for the peer-failure path)
+    inject = os.environ.get("FTL_INJECT_RANK_ERROR", "")
+    inject_rank_error = tuple(int(x) for x in inject.split(":")) if inject else None
+    agreed = False
     try:
         while training_step < args.training_steps:
             # ---- step boundary: the only place an interruption is acted on ----
-            code = env.max_int(flags.poll()) if env.distributed else flags.poll()
-            if code != STOP_NONE:
-                raise TrainingInterrupt(stop_code_to_error_type(code))
             if args.raise_error and training_step == args.error_step:
                 # fired *before* the step, so the saved state has exactly `error_step` updates;
                 # a job resumed from that very checkpoint does not re-fire on its first step
                 if not (args.checkpoint_id and training_step == first_step):
                     raise Exception("Simulated exception to test signal handler", -1)
+            if inject_rank_error == (env.rank, training_step):
+                raise RuntimeError(f"injected rank-local failure on rank {env.rank} at step {training_step}")
             if args.checkpoint_every and training_step > first_step and training_step % args.checkpoint_every == 0:
                 _save_now(trainer, args, training_step, stream, env)
                 logger.info(f"Periodic checkpoint saved at step {training_step}")
 
             input_ids, labels = next(stream)
-            loss = trainer.step(input_ids, labels)
+            # the step's single host collective: stop-flag agreement + global token count
+            code, n_items = env.step_sync(flags.poll(), int(labels.ne(-100).sum()))
+            if code != STOP_NONE:
+                agreed = True
+                raise TrainingInterrupt(stop_code_to_error_type(code))
+            loss = trainer.step(input_ids, labels, n_items=n_items)
 
             window_steps += 1
             if training_step == 1 or training_step % args.logging_frequency == 0:
@@ -148,6 +156,12 @@ def train(args) -> None:
         error_type = error_type_of(e)
         if error_type == -1 and not (len(e.args) >= 2 and e.args[1] == -1):
             logger.exception("Exception in the training loop")
+        if env.distributed and not agreed:
+            # this rank left the loop on its own (local exception, injected error, PeerAbort): pair with the peers'
+            # next step_sync so that they stop at the same boundary instead of waiting for this rank forever
+            if hasattr(trainer, "abort_peers") and error_type == -1:
+                trainer.abort_peers()      # peers' kernels parked in a device barrier fall through (status 2)
+            env.step_sync(STOP_ERROR, 0)
         training_step = _settle(trainer, stream, e, training_step, first_step, steps_base, batches_base, env)
         handle_exit(trainer.model, trainer.optimizer, trainer.lr_scheduler, training_step,
                     args.checkpoint_path, error_type, logger,
@@ -173,9 +187,8 @@ def _settle(trainer, stream, exc, training_step, first_step, steps_base, batches
     from .optim.lr import rewind_lr_scheduler
 
     if not hasattr(trainer, "committed_updates"):
+        stream.rewind(batches_base + (training_step - first_step))   # un-fetch the batch of the step that never ran
         return training_step
-    if env.distributed and not isinstance(exc, (TrainingInterrupt, PeerAbort)):
-        trainer.abort_peers()   # peers parked in a device barrier fall through instead of waiting for this rank
     done = first_step + trainer.committed_updates()
     done = env.max_int(-env.max_int(-done)) if env.distributed else done   # min over ranks (they agree; belt and braces)
     if done != training_step or trainer.optimizer.steps_done != steps_base + (done - first_step):

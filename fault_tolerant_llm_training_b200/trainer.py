@@ -50,9 +50,9 @@ class TorchTrainer:
         self.kernel_launches_per_step = 0
 
     # reference: train.py:93-110
-    def step(self, inputs: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
-        n_items = int(labels.ne(-100).sum())
-        n_items = self.env.sum_int(n_items)  # global count
+    def step(self, inputs: torch.Tensor, labels: torch.Tensor, n_items: Optional[int] = None) -> torch.Tensor:
+        if n_items is None:  # global count of unmasked tokens; train.py passes it from its step_sync
+            n_items = self.env.sum_int(int(labels.ne(-100).sum()))
         inputs = inputs.to(self.device, non_blocking=True)
         labels = labels.to(self.device, non_blocking=True)
         self.optimizer.zero_grad()

@@ -45,3 +45,18 @@ def test_two_rank_sigterm_saves_nothing(tmp_path):
     j = Job(tmp_path, 7101, _args(tmp_path, 500), nproc=2, signal_at=3, sig=signal.SIGTERM)
     assert "[EXIT HANDLER] Job cancelled, terminating." in j.text
     assert not os.path.exists(j.ckpt_path()) and j.sbatch_calls == []
+
+
+def test_rank_local_failure_stops_every_rank_at_the_same_step(tmp_path):
+    """One rank raises on its own: its peers learn about it through the step's single host
+    collective, everybody checkpoints the same step, nobody resubmits, and the job resumes."""
+    j = Job(tmp_path, 7201, _args(tmp_path, 12), nproc=2, extra_env={"FTL_INJECT_RANK_ERROR": "1:5"})
+    assert j.returncode == 0, j.text[-3000:]
+    assert "injected rank-local failure on rank 1 at step 5" in j.text
+    assert "[EXIT HANDLER] Error during training encountered, saving checkpoint." in j.text
+    assert "[EXIT HANDLER] Checkpoint saved at step 5" in j.text and j.sbatch_calls == []
+    ck = torch.load(j.ckpt_path(), weights_only=False)
+    assert ck["training_step"] == 5 and all(s["batches_consumed"] == 5 for s in ck["data_state"])
+    r = Job(tmp_path, 7202, _args(tmp_path, 12, "7201"), nproc=2)
+    assert "Resuming training from training_step 5" in r.text and "Training completed" in r.text
+    assert set(r.losses) == set(range(5, 12))
