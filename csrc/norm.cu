@@ -128,13 +128,24 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
     }
 }
 
-__global__ void rmsnorm_dw_finalize_kernel(const float* __restrict__ partial, int nparts, int dim,
-                                           __nv_bfloat16* __restrict__ dw) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= dim) return;
+// Fold the per-CTA partial rows: block = 32 columns x 8 row lanes; lane py adds partials py, py+8, ... in order,
+// the 8 lanes are then added in fixed order through shared memory (deterministic).  Reads are 128-byte coalesced.
+__global__ void __launch_bounds__(256)
+rmsnorm_dw_finalize_kernel(const float* __restrict__ partial, int nparts, int dim, __nv_bfloat16* __restrict__ dw) {
+    __shared__ float acc[8][33];
+    const int cx = threadIdx.x & 31, py = threadIdx.x >> 5;
+    const int j = blockIdx.x * 32 + cx;
     float s = 0.f;
-    for (int p = 0; p < nparts; ++p) s += partial[(int64_t)p * dim + j];  // fixed order
-    dw[j] = __float2bfloat16_rn(s);
+    if (j < dim)
+        for (int p = py; p < nparts; p += 8) s += partial[(int64_t)p * dim + j];
+    acc[py][cx] = s;
+    __syncthreads();
+    if (py == 0 && j < dim) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += acc[k][cx];
+        dw[j] = __float2bfloat16_rn(t);
+    }
 }
 
 static inline int norm_threads(int dim) {
@@ -176,7 +187,7 @@ FTL_API int ftl_rmsnorm_bwd(const void* dy, const void* x, const void* w, const 
     if (dres) rmsnorm_bwd_kernel<true><<<parts, threads, 0, stream>>>(DY, X, W, rstd, DR, DX, scratch, rows, dim);
     else rmsnorm_bwd_kernel<false><<<parts, threads, 0, stream>>>(DY, X, W, rstd, nullptr, DX, scratch, rows, dim);
     FTL_LAUNCH_CHECK();
-    rmsnorm_dw_finalize_kernel<<<(dim + 255) / 256, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw);
+    rmsnorm_dw_finalize_kernel<<<(dim + 31) / 32, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw);
     FTL_LAUNCH_CHECK();
     return 0;
 }
@@ -266,7 +277,7 @@ FTL_API int ftl_rmsnorm_bwd_static(const void* dy, const void* x, const void* w,
     else rmsnorm_bwd_kernel<false><<<parts, threads, 0, stream>>>(DY, X, W, rstd, nullptr, DX, scratch, rows, dim);
     e = cudaGetLastError();
     if (e == cudaSuccess) {
-        rmsnorm_dw_finalize_kernel<<<(dim + 255) / 256, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw);
+        rmsnorm_dw_finalize_kernel<<<(dim + 31) / 32, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw);
         e = cudaGetLastError();
     }
     if (e != cudaSuccess) snprintf(g_last_error, sizeof g_last_error, "ftl_rmsnorm_bwd_static: launch failed: %s", cudaGetErrorString(e));

@@ -30,13 +30,16 @@ def pytest_collection_modifyitems(config, items):
 def reference_modules():
     """The reference's own model.py / utils.py as oracles. Skipped when the
     reference tree is not mounted (e.g. on the GPU box)."""
-    if not os.path.isdir(REFERENCE_DIR):
+    ref_dir = REFERENCE_DIR
+    if not os.path.isdir(ref_dir):
+        ref_dir = os.path.join(ROOT, "baseline", "_ref")   # the pip --target install of the reference (travels to the GPU box)
+    if not os.path.exists(os.path.join(ref_dir, "model.py")):
         pytest.skip("reference tree not available")
     import importlib.util
 
     mods = {}
     for name in ("model", "utils"):
-        spec = importlib.util.spec_from_file_location(f"_ref_{name}", os.path.join(REFERENCE_DIR, f"{name}.py"))
+        spec = importlib.util.spec_from_file_location(f"_ref_{name}", os.path.join(ref_dir, f"{name}.py"))
         m = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(m)
         mods[name] = m

@@ -149,3 +149,35 @@ def test_nonfinite_step_is_not_committed():
         tr.model.output.weight[0, 0] = before[-1][0, 0]
     for p, q in zip(tr.model.parameters(), before):
         assert torch.equal(p, q)
+
+
+def test_loss_curve_tracks_the_reference_implementation(reference_modules):
+    """T4: same init, same batches — the B200 engine and the reference's own model.py + torch AdamW (with the
+    clipping the reference intended) follow the same loss curve within bf16 noise."""
+    m = reference_modules["model"]
+    tr = _trainer(lr=2e-3, warmup_steps=3)
+    args = m.TransformerModelArgs(dim=CFG.dim, n_layers=CFG.n_layers, n_heads=CFG.n_heads, n_kv_heads=CFG.n_kv_heads,
+                                  multiple_of=CFG.multiple_of, ffn_dim_multiplier=CFG.ffn_dim_multiplier,
+                                  norm_eps=CFG.norm_eps, rope_theta=CFG.rope_theta, seq_len=CFG.seq_len,
+                                  vocab_size=CFG.vocab_size)
+    with reference_modules["utils"].set_default_dtype(torch.bfloat16):
+        ref = m.Transformer(args)
+    ref.load_state_dict(tr.model.state_dict(), strict=True)
+    ref.cuda().train()
+    opt = torch.optim.AdamW(ref.parameters(), lr=2e-3)
+    sched = reference_modules["utils"].build_lr_scheduler(opt, 3)
+    ours, theirs = [], []
+    for s in range(12):
+        inputs, labels = _batch(s % 3)
+        ours.append(tr.step(inputs, labels).item())
+        opt.zero_grad()
+        logits = ref(inputs.cuda())
+        loss = torch.nn.functional.cross_entropy(logits.flatten(0, 1).float(), labels.cuda().flatten(0, 1), reduction="sum")
+        loss = loss / labels.ne(-100).sum()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(list(ref.parameters()), 1.0)
+        opt.step()
+        sched.step()
+        theirs.append(float(loss))
+    assert theirs[-1] < theirs[0] - 0.5                      # it actually trains
+    assert max(abs(a - b) for a, b in zip(ours, theirs)) < 0.08, (ours, theirs)

@@ -50,3 +50,32 @@ def test_gpu_sigterm_saves_nothing_and_exception_saves(tmp_path):
     assert os.path.isdir(k.ckpt_path().replace(".ckpt", ".shards")) and not os.path.exists(k.ckpt_path())
     r = Job(tmp_path, 6003, _args(tmp_path, 12, "6002"))   # resume straight from the shard directory
     assert "Resuming training from training_step 5" in r.text and "Training completed" in r.text
+
+
+def test_gpu_five_job_chain_seq8192_bitwise(tmp_path):
+    """BASELINE.json config 5 in miniature: seq 8192, a chain of 5 jobs (4 SIGUSR1 kills, each followed by the
+    resubmit that the fake sbatch records), packed dataset — loss curve and final model / optimizer / scheduler /
+    dataset state are bitwise those of one uninterrupted run."""
+    extra = ["--sequence-length", "8192", "--batch-size", "1", "--dataset-type", "packed", "--vocab-size", "2048"]
+    base = [a for a in GPU_ARGS]
+    for flag in ("--sequence-length", "--batch-size", "--vocab-size"):
+        i = base.index(flag)
+        del base[i:i + 2]
+    mk = lambda steps, *more: base + extra + ["--dataset", os.path.join(str(tmp_path), "data.parquet"),
+                                              "--training-steps", str(steps)] + list(more)
+    full = Job(tmp_path, 8000, mk(30, "--save-final"))
+    assert "Training completed" in full.text, full.text[-2000:]
+    prev, losses = None, {}
+    for hop in range(5):
+        last = hop == 4
+        more = ([str(prev)] if prev else []) + (["--save-final"] if last else [])
+        j = Job(tmp_path, 8001 + hop, mk(30, *more), signal_at=None if last else 5 + 6 * hop)
+        assert j.returncode == 0, j.text[-2000:]
+        if not last:
+            assert j.sbatch_calls[-1] == f"{tmp_path}/train.sh {8001 + hop}"
+        losses.update(j.losses)
+        prev = 8001 + hop
+    assert losses == full.losses
+    a = torch.load(full.ckpt_path(), weights_only=False)
+    b = torch.load(os.path.join(str(tmp_path), "checkpoints", f"checkpoint_{prev}.ckpt"), weights_only=False)
+    assert _digest(a) == _digest(b) and a["data_state"] == b["data_state"]
