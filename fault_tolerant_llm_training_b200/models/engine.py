@@ -400,6 +400,11 @@ class NativeTrainer:
         if dtype != torch.bfloat16:
             raise ValueError("the B200 engine is bf16-only (use --device cpu for other dtypes)")
         N.lib()  # fail loudly if the sm_100a library is missing
+        # Bitwise-reproducible steps are part of the contract (kill/resume chains must replay exactly).  Everything in
+        # csrc/ is deterministic by construction (fixed reduction orders, no float atomics); the one library op left
+        # on the path, SDPA's backward, accumulates dQ with atomics at long sequence lengths unless told otherwise.
+        if os.environ.get("FTL_DETERMINISTIC", "1") == "1":
+            torch.use_deterministic_algorithms(True, warn_only=True)
         self.cfg, self.env, self.device = cfg, env, env.device
         self.parallel = parallel
         self.grad_max_norm, self.clip_mode = float(grad_max_norm), clip_mode

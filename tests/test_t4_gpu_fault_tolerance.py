@@ -23,16 +23,17 @@ def _args(tmp, steps, *more):
 
 
 def test_gpu_usr1_chain_bitwise(tmp_path):
-    full = Job(tmp_path, 5000, _args(tmp_path, 24, "--save-final"))
+    # enough steps that the job is still running when the signal arrives (a step of this model takes ~2 ms)
+    full = Job(tmp_path, 5000, _args(tmp_path, 600, "--save-final"))
     assert full.returncode == 0 and "Training completed" in full.text, full.text[-2000:]
-    j1 = Job(tmp_path, 5001, _args(tmp_path, 24), signal_at=8, sig=signal.SIGUSR1)
+    j1 = Job(tmp_path, 5001, _args(tmp_path, 600), signal_at=8, sig=signal.SIGUSR1)
     assert j1.returncode == 0, j1.text[-2000:]
     assert "[EXIT HANDLER] Job timed out, saving checkpoint." in j1.text
     assert "shards durable in" in j1.text and "consolidated reference-layout file written" in j1.text
     assert j1.sbatch_calls == [f"{tmp_path}/train.sh 5001"]
     # durable (manifest) comes before the resubmit, the consolidated file after it
     assert j1.text.index("shards durable in") < j1.text.index("sbatch requeued") < j1.text.index("consolidated reference")
-    j2 = Job(tmp_path, 5002, _args(tmp_path, 24, "--save-final", "--checkpoint_id=5001"))
+    j2 = Job(tmp_path, 5002, _args(tmp_path, 600, "--save-final", "--checkpoint_id=5001"))
     assert j2.returncode == 0 and "Training completed" in j2.text, j2.text[-2000:]
     merged = dict(j1.losses); merged.update(j2.losses)
     assert merged == full.losses
@@ -63,13 +64,13 @@ def test_gpu_five_job_chain_seq8192_bitwise(tmp_path):
         del base[i:i + 2]
     mk = lambda steps, *more: base + extra + ["--dataset", os.path.join(str(tmp_path), "data.parquet"),
                                               "--training-steps", str(steps)] + list(more)
-    full = Job(tmp_path, 8000, mk(30, "--save-final"))
+    full = Job(tmp_path, 8000, mk(400, "--save-final"))
     assert "Training completed" in full.text, full.text[-2000:]
     prev, losses = None, {}
     for hop in range(5):
         last = hop == 4
         more = ([str(prev)] if prev else []) + (["--save-final"] if last else [])
-        j = Job(tmp_path, 8001 + hop, mk(30, *more), signal_at=None if last else 5 + 6 * hop)
+        j = Job(tmp_path, 8001 + hop, mk(400, *more), signal_at=None if last else 20 + 80 * hop)
         assert j.returncode == 0, j.text[-2000:]
         if not last:
             assert j.sbatch_calls[-1] == f"{tmp_path}/train.sh {8001 + hop}"
