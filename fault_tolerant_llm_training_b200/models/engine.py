@@ -186,6 +186,11 @@ class NativeEngine:
         self.qkv = [bf(T, self.qkv_dim) for _ in range(L)]
         self.attn = [None] * L                           # attention outputs (graph-holding tensors)
         self.attn_in = [None] * L
+        self.own_attn = self.ATTN_TC and seq % 128 == 0 and hd in (64, 128)
+        if self.own_attn:
+            self.attn_o = [bf(T, H * hd) for _ in range(L)]     # saved for the backward (delta, wo weight gradient)
+            self.attn_lse = [f32(batch * H * seq) for _ in range(L)]
+            self.attn_delta = f32(batch * H * seq)
         self.ao = bf(T, d)                               # wo output (consumed immediately)
         self.h = [bf(T, d) for _ in range(L)]
         self.hn = [bf(T, d) for _ in range(L)]
@@ -247,6 +252,9 @@ class NativeEngine:
     # step, with the RoPE / SwiGLU epilogues and the split reduction fused (0.97-1.20x cuBLAS on these shapes,
     # profiles/gemm_tc_pair_vs_cublas.jsonl).  FTL_GEMM=cublas: library GEMMs + separate elementwise kernels.
     USE_TC = os.environ.get("FTL_GEMM", "tc") != "cublas"
+    # FTL_ATTN=tc: the hand-written tcgen05 flash attention of csrc/attn_tc.cu (deterministic forward and backward,
+    # dq|dk|dv written in place with the inverse RoPE fused).  FTL_ATTN=lib: library SDPA through a small autograd island.
+    ATTN_TC = os.environ.get("FTL_ATTN", "tc") != "lib"
 
     def gemm_nt(self, a, b, out):
         if self.USE_TC:
@@ -272,6 +280,8 @@ class NativeEngine:
         c, B, S = self.cfg, self.B, self.S
         H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
         qkv = self.qkv[i]
+        if self.own_attn:
+            return N.attn_fwd(qkv, self.attn_o[i], self.attn_lse[i], B, S, H, KV, hd)
         q = qkv[:, :H * hd].view(B, S, H, hd).transpose(1, 2).detach().requires_grad_()
         k = qkv[:, H * hd:(H + KV) * hd].view(B, S, KV, hd).transpose(1, 2).detach().requires_grad_()
         v = qkv[:, (H + KV) * hd:].view(B, S, KV, hd).transpose(1, 2).detach().requires_grad_()
@@ -283,6 +293,10 @@ class NativeEngine:
     def _attention_bwd(self, i: int, dout: torch.Tensor) -> None:
         c, B, S = self.cfg, self.B, self.S
         H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        if self.own_attn:   # dq|dk|dv land in self.dqkv with the inverse rotary embedding already applied
+            N.attn_bwd(self.qkv[i], self.attn_o[i], dout, self.attn_lse[i], self.attn_delta, self.dqkv, B, S, H, KV, hd,
+                       self.cos, self.sin)
+            return
         o, (q, k, v) = self.attn[i], self.attn_in[i]
         do = dout.view(B, S, H, hd).transpose(1, 2)
         dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
@@ -367,11 +381,12 @@ class NativeEngine:
             N.rmsnorm_bwd(self.dtmp, self.h[i], lw["wfn"], self.rstd2[i], self.dh, lw["gfn"], self.norm_scratch,
                           dres=dx)
             # h = x + wo(attn)
-            a = self.attn[i].transpose(1, 2).reshape(T, H * hd)
+            a = self.attn_o[i] if self.own_attn else self.attn[i].transpose(1, 2).reshape(T, H * hd)
             self.gemm_tn(self.dh, a, lw["go"])
             self.gemm_nn(self.dh, lw["wo"], self.dattn)
             self._attention_bwd(i, self.dattn)
-            N.rope_inplace(self.dqkv, self.cos, self.sin, self.S, rot, hd, inverse=True)
+            if not self.own_attn:
+                N.rope_inplace(self.dqkv, self.cos, self.sin, self.S, rot, hd, inverse=True)
             self.gemm_tn(self.dqkv, self.xn[i], lw["gqkv"])
             self.gemm_nn(self.dqkv, lw["wqkv"], self.dtmp)
             N.rmsnorm_bwd(self.dtmp, self.x[i], lw["wan"], self.rstd1[i], spare, lw["gan"], self.norm_scratch,

@@ -82,6 +82,8 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_gemm_swiglu_gather", [P, I64, P, P, I64, P, P, P, I64, I, I, I, P, I64, I64, I, I, I, P, P])
     _sig(L, "ftl_fsdp_gather", [P, I64, P, I64, I, I, P, I, P])
     _sig(L, "ftl_adamw_shard", [P, P, P, P, I64, P, P, P, P, I, P])
+    _sig(L, "ftl_attn_fwd", [P, I64, P, I64, P, I, I, I, I, I, P])
+    _sig(L, "ftl_attn_bwd", [P, I64, P, P, I64, P, P, P, P, P, I, I, I, I, I, P])
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -384,3 +386,24 @@ def adamw_shard(p, g, m, v, hyper, stats, status, commits=None, max_ctas=0):
     _bf16(p, g, m, v)
     _check(lib().ftl_adamw_shard(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), _ptr(hyper), _ptr(stats), _ptr(status),
                                  _ptr(commits), max_ctas, _stream()), "ftl_adamw_shard")
+
+
+# ---- tcgen05 flash attention (csrc/attn_tc.cu) -----------------------------------------------------------
+def attn_fwd(qkv, out, lse, B, S, H, KV, hd):
+    """Causal GQA attention read in place from the fused [B*S, (H+2KV)*hd] projection (RoPE already applied).
+    out: [B*S, H*hd] bf16; lse: fp32 [B, H, S] (log2 domain), kept for the backward."""
+    _mat(qkv), _mat(out)
+    assert lse.dtype == torch.float32 and lse.numel() == B * H * S
+    _check(lib().ftl_attn_fwd(_ptr(qkv), qkv.stride(0), _ptr(out), out.stride(0), _ptr(lse), B, S, H, KV, hd, _stream()),
+           "ftl_attn_fwd")
+    return out
+
+
+def attn_bwd(qkv, out, d_out, lse, delta, dqkv, B, S, H, KV, hd, cos=None, sin=None):
+    """Deterministic backward: writes dq | dk | dv into dqkv ([B*S, (H+2KV)*hd]); with cos/sin the inverse rotary
+    embedding is applied to dq and dk, so dqkv is the gradient of the un-rotated projection."""
+    _mat(qkv), _mat(out), _mat(d_out), _mat(dqkv)
+    assert out.stride(0) == d_out.stride(0) and dqkv.stride(0) == qkv.stride(0) and delta.numel() == B * H * S
+    _check(lib().ftl_attn_bwd(_ptr(qkv), qkv.stride(0), _ptr(out), _ptr(d_out), out.stride(0), _ptr(lse), _ptr(delta),
+                              _ptr(dqkv), _ptr(cos), _ptr(sin), B, S, H, KV, hd, _stream()), "ftl_attn_bwd", 3)
+    return dqkv

@@ -205,3 +205,37 @@ def test_gemm_tc_qkv_rope_epilogue(N):
     ref_rot = T.rope_apply(ref[:, :rot].reshape(B, S, H + KV, hd), cos, sin).reshape(M, rot)
     assert _rel(out[:, :rot], ref_rot.float()) < 5e-3
     assert _rel(out[:, rot:], ref[:, rot:].float()) < 5e-3
+
+
+# ---- tcgen05 flash attention (csrc/attn_tc.cu) vs the explicit fp32 softmax(QK^T)V oracle and its autograd ----
+@pytest.mark.parametrize("B,S,H,KV,hd", [(2, 256, 4, 2, 64), (1, 384, 4, 2, 128), (1, 256, 2, 2, 128)])
+def test_attention_tc_fwd_bwd_deterministic(N, B, S, H, KV, hd):
+    W = (H + 2 * KV) * hd
+    qkv, dout = bf(B * S, W, scale=0.7, seed=1), bf(B * S, H * hd, scale=0.5, seed=2)
+    out = torch.empty(B * S, H * hd, device=DEV, dtype=torch.bfloat16)
+    lse, delta = torch.empty(B * H * S, device=DEV), torch.empty(B * H * S, device=DEV)
+    dqkv = torch.zeros_like(qkv)
+    N.attn_fwd(qkv, out, lse, B, S, H, KV, hd)
+    N.attn_bwd(qkv, out, dout, lse, delta, dqkv, B, S, H, KV, hd)
+    qf = qkv.float().view(B, S, H + 2 * KV, hd)
+    q, k, v = (t.clone().requires_grad_() for t in (qf[:, :, :H], qf[:, :, H:H + KV], qf[:, :, H + KV:]))
+    ref = T.attention_fp32_oracle(q, k, v)
+    ref.backward(dout.float().view(B, S, H, hd))
+    d4 = dqkv.view(B, S, -1, hd)
+    assert _rel(out.view(B, S, H, hd), ref.detach()) < 1e-2
+    assert _rel(d4[:, :, :H], q.grad) < 1e-2 and _rel(d4[:, :, H:H + KV], k.grad) < 1e-2 and _rel(d4[:, :, H + KV:], v.grad) < 1e-2
+    # natural-log lse of the scaled scores
+    sc = torch.einsum("bqhd,bkhd->bhqk", q.detach(), k.detach().repeat_interleave(H // KV, dim=2)) / hd ** 0.5
+    sc = sc.masked_fill(~torch.ones(S, S, dtype=torch.bool, device=DEV).tril(), float("-inf"))
+    torch.testing.assert_close(lse.view(B, H, S) * 0.6931471805599453, torch.logsumexp(sc, -1), rtol=1e-3, atol=1e-3)
+    # bitwise repeatable, and the fused inverse RoPE equals rotating the gradients afterwards
+    out2, dq2 = torch.empty_like(out), torch.zeros_like(dqkv)
+    N.attn_fwd(qkv, out2, lse, B, S, H, KV, hd)
+    N.attn_bwd(qkv, out2, dout, lse, delta, dq2, B, S, H, KV, hd)
+    assert torch.equal(out, out2) and torch.equal(dqkv, dq2)
+    cos, sin = T.rope_table(hd, S, 500000.0, device=DEV)
+    dq3 = torch.zeros_like(dqkv)
+    N.attn_bwd(qkv, out, dout, lse, delta, dq3, B, S, H, KV, hd, cos, sin)
+    want = dqkv.clone()
+    N.rope_inplace(want, cos, sin, S, (H + KV) * hd, hd, inverse=True)
+    torch.testing.assert_close(dq3.float(), want.float(), rtol=2e-2, atol=2e-3)
