@@ -18,7 +18,9 @@
 //   attn_bwd_dq       CTA = (batch, q head, 128-query tile); loops over 64-key tiles: S = Q K^T, dP = dO V^T ->
 //                     dS (thread = query row) to smem -> dQ += dS K accumulated in TMEM.
 //   attn_delta        delta[t, h] = sum_d dO * O   (fp32), the softmax-backward row term.
-// Warp roles as in the GEMM: warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2-5 = 128 math threads.
+// Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2-9 = 256 math threads: TMEM lane quarter
+// warp % 4 (a hardware rule), column half (warp - 2) / 4, so every tile row is served by two threads on different
+// schedulers and TMEM / MUFU latency of one hides behind the other.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cudaTypedefs.h>
@@ -31,7 +33,7 @@
 
 namespace ftl {
 
-constexpr int kAttnThreads = 192;
+constexpr int kAttnThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2-9: two math threads per tile row (each owns half the columns)
 constexpr float kLog2e = 1.4426950408889634f;
 
 // ---- swizzled shared-memory tiles -----------------------------------------------------------------------------
@@ -65,31 +67,58 @@ struct AttnArgs {
     int B, S, H, KV, ld_qkv;
     float scale_log2;              // 1/sqrt(hd) * log2(e)
     float scale;                   // 1/sqrt(hd)
+    // dK/dV kernel work split: an item (batch, kv head, key tile) loops over rep * (#query tiles) inner iterations, from
+    // 8 (last key tile) to 4 * S/64 (first); items longer than chunk_len are cut into chunks that run as separate
+    // units and leave fp32 partials in `partial`, which attn_dkv_reduce folds in chunk order (deterministic).
+    int chunk_len, units;
+    float* partial;                // [units][2][128][hd] fp32
 };
 
+// unit -> (batch, kv head, key tile, inner range [n0, n1), whether the unit is the whole item)
+__device__ __forceinline__ void dkv_decode(const AttnArgs& a, int u, int rep, int q_tiles64, int k_tiles, int& b, int& g,
+                                           int& kt, int& n0, int& n1, bool& whole) {
+    const int bg = u % (a.B * a.KV);
+    int v = u / (a.B * a.KV);
+    b = bg / a.KV; g = bg % a.KV;
+    kt = 0; n0 = 0; n1 = 0; whole = true;
+    for (int k = 0; k < k_tiles; ++k) {           // key tile 0 has the longest loop: heavy units come first
+        const int inner = rep * (q_tiles64 - 2 * k);
+        const int nc = (inner + a.chunk_len - 1) / a.chunk_len;
+        if (v < nc) {
+            kt = k; n0 = v * a.chunk_len; n1 = n0 + a.chunk_len < inner ? n0 + a.chunk_len : inner; whole = nc == 1;
+            return;
+        }
+        v -= nc;
+    }
+}
+
 // ================================================================================================= forward
+// Software pipeline (per CTA): the MMA warp issues S(j+1) as soon as K(j+1) has landed, i.e. while the math threads
+// are still in the softmax of tile j; P and the O tile are double-buffered, and the math threads fold O(j-1) into
+// their registers only after they have published P(j), so P V (j) runs under that accumulation and under softmax(j+1).
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
     constexpr int BM = 128, BN = 128;
     constexpr int kQBytes = BM * HD * 2, kKBytes = BN * HD * 2, kPBytes = BM * BN * 2;
-    constexpr int kTmemO = 2 * BN;                    // columns: S0 [0,128) S1 [128,256) O [256, 256+HD)
+    constexpr int kTmemO = 2 * BN;                    // columns: S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
     uint8_t* sK = sQ + kQBytes;                       // 2 stages
     uint8_t* sV = sK + 2 * kKBytes;                   // 2 stages
-    uint8_t* sP = sV + 2 * kKBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);
+    uint8_t* sP = sV + 2 * kKBytes;                   // 2 buffers
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kPBytes);
+    float* sMax = reinterpret_cast<float*>(bars + 16);   // [2][BM] row-max / row-sum exchange between the column halves
     uint64_t* q_full = bars;          // 1
     uint64_t* q_empty = bars + 1;     // 1
     uint64_t* kv_full = bars + 2;     // 2
     uint64_t* kv_empty = bars + 4;    // 2
     uint64_t* s_full = bars + 6;      // 2
-    uint64_t* p_full = bars + 8;      // 1
-    uint64_t* o_full = bars + 9;      // 1
-    uint64_t* o_empty = bars + 10;    // 1
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+    uint64_t* p_full = bars + 8;      // 2
+    uint64_t* o_full = bars + 10;     // 2
+    uint64_t* o_empty = bars + 12;    // 2
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q_tiles = a.S / BM;
@@ -99,8 +128,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmQKV);
         ptx::mbar_init(q_full, 1); ptx::mbar_init(q_empty, 1);
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); ptx::mbar_init(&s_full[i], 1); }
-        ptx::mbar_init(p_full, 4); ptx::mbar_init(o_full, 1); ptx::mbar_init(o_empty, 4);
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); ptx::mbar_init(&s_full[i], 1);
+            ptx::mbar_init(&p_full[i], 8); ptx::mbar_init(&o_full[i], 1); ptx::mbar_init(&o_empty[i], 8);
+        }
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
@@ -143,130 +174,139 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
     } else if (warp == 1) {
         constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(BM, BN, false, false);
         constexpr uint32_t idesc_o = ptx::umma_idesc_bf16(BM, HD, false, true);   // B = V is MN-major
-        int kv_it = 0, q_it = 0, s_it = 0, p_it = 0, o_it = 0;
+        int t_it = 0, q_it = 0;                                                    // t_it: global tile counter
         for (int it = blockIdx.x; it < items; it += gridDim.x, ++q_it) {
             int b, h, qt; decode(it, b, h, qt);
             ptx::mbar_wait(q_full, q_it & 1);
             const int nkv = qt + 1;
-            auto issue_s = [&](int kv_index, int s_index) {
-                const int st = kv_index & 1;
-                ptx::mbar_wait(&kv_full[st], (kv_index >> 1) & 1);
+            auto issue_s = [&](int t) {                                            // scores of global tile t
+                const int st = t & 1;
+                ptx::mbar_wait(&kv_full[st], (t >> 1) & 1);
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
                     const uint32_t qa = ptx::smem_u32(sQ), kb = ptx::smem_u32(sK + st * kKBytes);
 #pragma unroll
                     for (int k = 0; k < HD / 16; ++k)
-                        ptx::umma_bf16(tmem + (s_index & 1) * BN, desc_kmajor(qa, BM, k), desc_kmajor(kb, BN, k), idesc_s, k != 0);
-                    ptx::umma_commit(&s_full[s_index & 1]);
+                        ptx::umma_bf16(tmem + st * BN, desc_kmajor(qa, BM, k), desc_kmajor(kb, BN, k), idesc_s, k != 0);
+                    ptx::umma_commit(&s_full[st]);
                 }
                 __syncwarp();
             };
-            issue_s(kv_it, s_it);
-            for (int j = 0; j < nkv; ++j) {
-                if (j + 1 < nkv) issue_s(kv_it + 1, s_it + 1);       // next scores while the softmax of this tile runs
-                ptx::mbar_wait(p_full, p_it & 1); ++p_it;             // P(j) is in smem, S(j) has been read
-                ptx::mbar_wait(o_empty, (o_it & 1) ^ 1);              // O_tile(j-1) has been read
+            issue_s(t_it);
+            for (int j = 0; j < nkv; ++j, ++t_it) {
+                if (j + 1 < nkv) issue_s(t_it + 1);                   // next scores while the softmax of this tile runs
+                const int st = t_it & 1, ph = (t_it >> 1) & 1;
+                ptx::mbar_wait(&p_full[st], ph);                      // P(t) is in smem, S(t) has been read
+                ptx::mbar_wait(&o_empty[st], ph ^ 1);                 // O buffer st (tile t-2) has been folded
                 ptx::tc_fence_after();
-                const int st = kv_it & 1;
                 if (ptx::elect_one()) {
-                    const uint32_t pa = ptx::smem_u32(sP), vb = ptx::smem_u32(sV + st * kKBytes);
+                    const uint32_t pa = ptx::smem_u32(sP + st * kPBytes), vb = ptx::smem_u32(sV + st * kKBytes);
 #pragma unroll
                     for (int k = 0; k < BN / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmemO, desc_kmajor(pa, BM, k), desc_mnmajor(vb, BN, k), idesc_o, k != 0);
-                    ptx::umma_commit(o_full);
+                        ptx::umma_bf16(tmem + kTmemO + st * BN, desc_kmajor(pa, BM, k), desc_mnmajor(vb, BN, k), idesc_o, k != 0);
+                    ptx::umma_commit(&o_full[st]);
                     ptx::umma_commit(&kv_empty[st]);
                     if (j == nkv - 1) ptx::umma_commit(q_empty);
                 }
                 __syncwarp();
-                ++o_it; ++kv_it; ++s_it;
             }
         }
     } else {
-        const int q = warp & 3;
+        const int q = warp & 3, half = (warp - 2) >> 2;                // TMEM lane quarter, column half
         const int r = q * 32 + lane;                                   // query row inside the tile = TMEM lane
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-        int s_it = 0, o_it = 0;
+        constexpr int CW = BN / 2, OW = HD / 2;                        // score / output columns owned by this thread
+        const int c0 = half * CW, d0 = half * OW;
+        int t_it = 0;
         for (int it = blockIdx.x; it < items; it += gridDim.x) {
             int b, h, qt; decode(it, b, h, qt);
             const int qi = qt * BM + r;
-            float m = -INFINITY, l = 0.f;
-            float acc[HD];
+            float m = -INFINITY, l = 0.f, alpha_prev = 0.f;
+            float acc[OW];
 #pragma unroll
-            for (int d = 0; d < HD; ++d) acc[d] = 0.f;
-            for (int j = 0; j <= qt; ++j, ++s_it, ++o_it) {
-                ptx::mbar_wait(&s_full[s_it & 1], (s_it >> 1) & 1);
+            for (int d = 0; d < OW; ++d) acc[d] = 0.f;
+            auto fold = [&](int t, float alpha) {                      // acc = acc * alpha + O(t)[:, d0 : d0 + OW]
+                const int st = t & 1;
+                ptx::mbar_wait(&o_full[st], (t >> 1) & 1);
                 ptx::tc_fence_after();
-                const uint32_t ts = tmem + (s_it & 1) * BN + lane_addr;
-                const bool diag = j == qt;
-                // pass 1: row maximum
-                float mx = -INFINITY;
-#pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
+#pragma unroll
+                for (int c = 0; c < OW; c += 32) {
                     uint32_t v[32];
-                    ptx::tmem_ld32(ts + c, v);
+                    ptx::tmem_ld32(tmem + kTmemO + st * BN + lane_addr + d0 + c, v);
                     ptx::tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const float s = __uint_as_float(v[i]);
-                        if (!diag || j * BN + c + i <= qi) mx = fmaxf(mx, s);
-                    }
+                    for (int i = 0; i < 32; ++i) acc[c + i] = fmaf(acc[c + i], alpha, __uint_as_float(v[i]));
                 }
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&o_empty[st]);
+            };
+            for (int j = 0; j <= qt; ++j, ++t_it) {
+                const int st = t_it & 1;
+                ptx::mbar_wait(&s_full[st], (t_it >> 1) & 1);
+                ptx::tc_fence_after();
+                const uint32_t ts = tmem + st * BN + lane_addr + c0;
+                const bool diag = j == qt;
+                const int lim = diag ? r - c0 : CW;                     // local columns <= lim are visible
+                // this thread's half of the score row stays in registers between the two passes
+                uint32_t v[CW];
+#pragma unroll
+                for (int c = 0; c < CW; c += 32) ptx::tmem_ld32(ts + c, *reinterpret_cast<uint32_t(*)[32]>(&v[c]));
+                ptx::tmem_ld_wait();
+                float mx = -INFINITY;
+                if (!diag) {
+#pragma unroll
+                    for (int i = 0; i < CW; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+                } else {
+#pragma unroll
+                    for (int i = 0; i < CW; ++i) if (i <= lim) mx = fmaxf(mx, __uint_as_float(v[i]));
+                }
+                // row maximum = max over the two halves: exchange through shared memory
+                sMax[half * BM + r] = mx;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                mx = fmaxf(mx, sMax[(half ^ 1) * BM + r]);
+                asm volatile("bar.sync 1, 256;" ::: "memory");          // all reads done before the next tile's writes
                 const float m_new = fmaxf(m, mx * a.scale_log2);
                 const float alpha = exp2f(m - m_new);                   // m = -inf on the first tile -> 0
-                // pass 2: probabilities -> bf16 -> swizzled smem (A operand of P V), row sum
                 float sum = 0.f;
-                const uint32_t pbase = ptx::smem_u32(sP);
-#pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
-                    uint32_t v[32];
-                    ptx::tmem_ld32(ts + c, v);
-                    ptx::tmem_ld_wait();
+                const uint32_t pbase = ptx::smem_u32(sP + st * kPBytes);
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        float p[8];
+                for (int u = 0; u < CW / 8; ++u) {
+                    float p[8];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int col = c + u * 8 + i;
-                            float e = exp2f(__uint_as_float(v[u * 8 + i]) * a.scale_log2 - m_new);
-                            if (diag && j * BN + col > qi) e = 0.f;
-                            p[i] = round_bf16(e);
-                            sum += p[i];
-                        }
-                        st_shared16(sw128_addr(pbase, BM, r, c + u * 8), pack8(p));
+                    for (int i = 0; i < 8; ++i) {
+                        float e = exp2f(fmaf(__uint_as_float(v[u * 8 + i]), a.scale_log2, -m_new));
+                        if (diag && u * 8 + i > lim) e = 0.f;
+                        p[i] = e;
+                        sum += e;
                     }
+                    st_shared16(sw128_addr(pbase, BM, r, c0 + u * 8), pack8(p));
                 }
-                l = l * alpha + sum;
+                l = fmaf(l, alpha, sum);                                // partial over this thread's columns
                 m = m_new;
                 ptx::tc_fence_before();
                 ptx::fence_proxy_async();                               // generic-proxy smem writes -> UMMA (async proxy)
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(p_full);
-                // O += P V
-                ptx::mbar_wait(o_full, o_it & 1);
-                ptx::tc_fence_after();
-#pragma unroll
-                for (int c = 0; c < HD; c += 32) {
-                    uint32_t v[32];
-                    ptx::tmem_ld32(tmem + kTmemO + lane_addr + c, v);
-                    ptx::tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) acc[c + i] = acc[c + i] * alpha + __uint_as_float(v[i]);
-                }
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(o_empty);
+                if (lane == 0) ptx::mbar_arrive(&p_full[st]);
+                if (j > 0) fold(t_it - 1, alpha_prev);                  // runs while the tensor core does P V of this tile
+                alpha_prev = alpha;
             }
-            // finalize: O / l, lse
+            fold(t_it - 1, alpha_prev);
+            // finalize: the two halves add their partial row sums, then O / l and the lse
+            sMax[half * BM + r] = l;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            l += sMax[(half ^ 1) * BM + r];
             const float inv = 1.f / l;
-            __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD;
+            __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD + d0;
 #pragma unroll
-            for (int d = 0; d < HD; d += 8) {
+            for (int d = 0; d < OW; d += 8) {
                 float o[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) o[i] = acc[d + i] * inv;
                 st8(orow + d, pack8(o));
             }
-            a.lse[((int64_t)b * a.H + h) * a.S + qi] = m + log2f(l);
+            if (half == 0) a.lse[((int64_t)b * a.H + h) * a.S + qi] = m + log2f(l);
+            asm volatile("bar.sync 1, 256;" ::: "memory");              // exchange buffer free again for the next item
         }
     }
     ptx::tc_fence_before();
@@ -317,39 +357,42 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     const __grid_constant__ CUtensorMap tmDO64, const AttnArgs a) {
     constexpr int BK = 128, BQ = 64;                   // key tile (UMMA M), query tile (UMMA N)
     constexpr int kKBytes = BK * HD * 2, kQBytes = BQ * HD * 2, kTBytes = BK * BQ * 2;
-    constexpr int kTmS = 0, kTmDP = 64, kTmDV = 128, kTmDK = 128 + HD;
+    constexpr int kTmDP = 64, kTmDV = 256, kTmDK = 256 + HD;   // S / dP of buffer b at b*128 and b*128 + 64
+    constexpr int NQ = 3;      // Q / dO stages: the TMA loads run two iterations ahead of the MMAs that consume them
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem;
     uint8_t* sV = sK + kKBytes;
-    uint8_t* sQ = sV + kKBytes;                        // 2 stages of [BQ x HD]
-    uint8_t* sDO = sQ + 2 * kQBytes;                   // 2 stages
-    uint8_t* sPT = sDO + 2 * kQBytes;                  // P^T  [BK x BQ]
-    uint8_t* sDST = sPT + kTBytes;                     // dS^T [BK x BQ]
-    float* sLse = reinterpret_cast<float*>(sDST + kTBytes);   // 2 x BQ
+    uint8_t* sQ = sV + kKBytes;                        // NQ stages of [BQ x HD]
+    uint8_t* sDO = sQ + NQ * kQBytes;                  // NQ stages
+    uint8_t* sPT = sDO + NQ * kQBytes;                 // P^T  [BK x BQ], 2 buffers
+    uint8_t* sDST = sPT + 2 * kTBytes;                 // dS^T [BK x BQ], 2 buffers
+    float* sLse = reinterpret_cast<float*>(sDST + 2 * kTBytes);   // 2 x BQ
     float* sDelta = sLse + 2 * BQ;                            // 2 x BQ
     uint64_t* bars = reinterpret_cast<uint64_t*>(sDelta + 2 * BQ);
     uint64_t* kv_full = bars;        // 1
     uint64_t* kv_empty = bars + 1;   // 1
-    uint64_t* q_full = bars + 2;     // 2
-    uint64_t* q_empty = bars + 4;    // 2
-    uint64_t* s_full = bars + 6;     // 1  (S^T and dP^T ready)
-    uint64_t* t_full = bars + 7;     // 1  (P^T, dS^T in smem; S/dP TMEM read)
-    uint64_t* t_empty = bars + 8;    // 1  (dV/dK MMAs that read P^T/dS^T have retired)
-    uint64_t* acc_full = bars + 9;   // 1
-    uint64_t* acc_empty = bars + 10; // 1
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+    uint64_t* q_full = bars + 2;     // NQ (<= 4)
+    uint64_t* q_empty = bars + 6;    // NQ
+    uint64_t* s_full = bars + 10;    // 2  (S^T and dP^T of buffer b ready)
+    uint64_t* t_full = bars + 12;    // 2  (P^T, dS^T of buffer b in smem; its S/dP TMEM read)
+    uint64_t* t_empty = bars + 14;   // 2  (dV/dK MMAs that read buffer b have retired)
+    uint64_t* acc_full = bars + 16;  // 1
+    uint64_t* acc_empty = bars + 17; // 1
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k_tiles = a.S / BK, rep = a.H / a.KV;
-    const int items = a.B * a.KV * k_tiles;
+    const int items = a.units;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmQKV);
         ptx::mbar_init(kv_full, 1); ptx::mbar_init(kv_empty, 1);
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&q_full[i], 1); ptx::mbar_init(&q_empty[i], 1); }
-        ptx::mbar_init(s_full, 1); ptx::mbar_init(t_full, 4); ptx::mbar_init(t_empty, 1);
-        ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_empty, 4);
+        for (int i = 0; i < NQ; ++i) { ptx::mbar_init(&q_full[i], 1); ptx::mbar_init(&q_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&t_full[i], 8); ptx::mbar_init(&t_empty[i], 1);
+        }
+        ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_empty, 8);
         ptx::fence_barrier_init();
     }
     if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
@@ -358,19 +401,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     ptx::tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    auto decode = [&](int it, int& b, int& g, int& kt) {     // small kt (long query loops) first
-        kt = it / (a.B * a.KV);
-        const int r = it % (a.B * a.KV);
-        b = r / a.KV; g = r % a.KV;
-    };
-    // inner iterations of an item: for hh in 0..rep-1, for qtile in first..last   (BQ = 64: two per 128-key tile row)
+    // inner iteration n of an item: query head g*rep + n / nq, 64-query tile 2*kt + n % nq, nq = S/64 - 2*kt
     const int q_tiles64 = a.S / BQ;
 
     if (warp == 0) {
         if (ptx::elect_one()) {
             int item_it = 0, q_it = 0;
             for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
-                int b, g, kt; decode(it, b, g, kt);
+                int b, g, kt, n0, n1; bool whole;
+                dkv_decode(a, it, rep, q_tiles64, k_tiles, b, g, kt, n0, n1, whole);
                 ptx::mbar_wait(kv_empty, (item_it & 1) ^ 1);
                 ptx::mbar_arrive_expect_tx(kv_full, 2 * kKBytes);
                 const int krow = b * a.S + kt * BK;
@@ -379,18 +418,17 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     ptx::tma_load_2d(sK + c * BK * 128, &tmQKV, kv_full, (a.H + g) * HD + c * 64, krow);
                     ptx::tma_load_2d(sV + c * BK * 128, &tmQKV, kv_full, (a.H + a.KV + g) * HD + c * 64, krow);
                 }
-                for (int hh = 0; hh < rep; ++hh) {
-                    const int h = g * rep + hh;
-                    for (int qt = kt * (BK / BQ); qt < q_tiles64; ++qt, ++q_it) {
-                        const int st = q_it & 1;
-                        ptx::mbar_wait(&q_empty[st], ((q_it >> 1) & 1) ^ 1);
-                        ptx::mbar_arrive_expect_tx(&q_full[st], 2 * kQBytes);
-                        const int qrow = b * a.S + qt * BQ;
+                const int nq = q_tiles64 - 2 * kt;
+                for (int n = n0; n < n1; ++n, ++q_it) {
+                    const int h = g * rep + n / nq, qt = 2 * kt + n % nq;
+                    const int st = q_it % NQ;
+                    ptx::mbar_wait(&q_empty[st], ((q_it / NQ) & 1) ^ 1);
+                    ptx::mbar_arrive_expect_tx(&q_full[st], 2 * kQBytes);
+                    const int qrow = b * a.S + qt * BQ;
 #pragma unroll
-                        for (int c = 0; c < HD / 64; ++c) {
-                            ptx::tma_load_2d(sQ + st * kQBytes + c * BQ * 128, &tmQKV64, &q_full[st], h * HD + c * 64, qrow);
-                            ptx::tma_load_2d(sDO + st * kQBytes + c * BQ * 128, &tmDO64, &q_full[st], h * HD + c * 64, qrow);
-                        }
+                    for (int c = 0; c < HD / 64; ++c) {
+                        ptx::tma_load_2d(sQ + st * kQBytes + c * BQ * 128, &tmQKV64, &q_full[st], h * HD + c * 64, qrow);
+                        ptx::tma_load_2d(sDO + st * kQBytes + c * BQ * 128, &tmDO64, &q_full[st], h * HD + c * 64, qrow);
                     }
                 }
             }
@@ -398,41 +436,49 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     } else if (warp == 1) {
         constexpr uint32_t idesc_st = ptx::umma_idesc_bf16(BK, BQ, false, false);   // S^T = K Q^T, dP^T = V dO^T
         constexpr uint32_t idesc_acc = ptx::umma_idesc_bf16(BK, HD, false, true);   // dV = P^T dO, dK = dS^T Q (B MN-major)
-        int item_it = 0, q_it = 0, n_it = 0;
+        int item_it = 0, n_it = 0;                                      // n_it: global inner-iteration counter
+        const uint32_t ka = ptx::smem_u32(sK), va = ptx::smem_u32(sV);
+        // S^T / dP^T of inner iteration t go to TMEM buffer t & 1 and read Q / dO stage t & 1
+        auto issue_sdp = [&](int t) {
+            const int st = t & 1, qs = t % NQ;
+            ptx::mbar_wait(&q_full[qs], (t / NQ) & 1);
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+                const uint32_t qb = ptx::smem_u32(sQ + qs * kQBytes), dob = ptx::smem_u32(sDO + qs * kQBytes);
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    ptx::umma_bf16(tmem + st * 128, desc_kmajor(ka, BK, k), desc_kmajor(qb, BQ, k), idesc_st, k != 0);
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    ptx::umma_bf16(tmem + st * 128 + kTmDP, desc_kmajor(va, BK, k), desc_kmajor(dob, BQ, k), idesc_st, k != 0);
+                ptx::umma_commit(&s_full[st]);
+            }
+            __syncwarp();
+        };
         for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
-            int b, g, kt; decode(it, b, g, kt);
+            int b, g, kt, n0, n1; bool whole;
+            dkv_decode(a, it, rep, q_tiles64, k_tiles, b, g, kt, n0, n1, whole);
             ptx::mbar_wait(kv_full, item_it & 1);
             ptx::mbar_wait(acc_empty, (item_it & 1) ^ 1);
-            const int inner = rep * (q_tiles64 - kt * (BK / BQ));
-            for (int n = 0; n < inner; ++n, ++q_it, ++n_it) {
-                const int st = q_it & 1;
-                ptx::mbar_wait(&q_full[st], (q_it >> 1) & 1);
-                ptx::mbar_wait(t_empty, (n_it & 1) ^ 1);   // previous dV/dK MMAs retired: S/dP TMEM and P^T/dS^T smem are free
-                ptx::tc_fence_after();
-                const uint32_t ka = ptx::smem_u32(sK), va = ptx::smem_u32(sV);
-                const uint32_t qb = ptx::smem_u32(sQ + st * kQBytes), dob = ptx::smem_u32(sDO + st * kQBytes);
-                if (ptx::elect_one()) {
-#pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmS, desc_kmajor(ka, BK, k), desc_kmajor(qb, BQ, k), idesc_st, k != 0);
-#pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmDP, desc_kmajor(va, BK, k), desc_kmajor(dob, BQ, k), idesc_st, k != 0);
-                    ptx::umma_commit(s_full);
-                }
-                __syncwarp();
-                ptx::mbar_wait(t_full, n_it & 1);
+            const int inner = n1 - n0;
+            issue_sdp(n_it);
+            for (int n = 0; n < inner; ++n, ++n_it) {
+                if (n + 1 < inner) issue_sdp(n_it + 1);               // next scores run under the math of this iteration
+                const int st = n_it & 1;
+                ptx::mbar_wait(&t_full[st], (n_it >> 1) & 1);
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
-                    const uint32_t pt = ptx::smem_u32(sPT), dst = ptx::smem_u32(sDST);
+                    const int qs = n_it % NQ;
+                    const uint32_t qb = ptx::smem_u32(sQ + qs * kQBytes), dob = ptx::smem_u32(sDO + qs * kQBytes);
+                    const uint32_t pt = ptx::smem_u32(sPT + st * kTBytes), dst = ptx::smem_u32(sDST + st * kTBytes);
 #pragma unroll
                     for (int k = 0; k < BQ / 16; ++k)
                         ptx::umma_bf16(tmem + kTmDV, desc_kmajor(pt, BK, k), desc_mnmajor(dob, BQ, k), idesc_acc, (n | k) != 0);
 #pragma unroll
                     for (int k = 0; k < BQ / 16; ++k)
                         ptx::umma_bf16(tmem + kTmDK, desc_kmajor(dst, BK, k), desc_mnmajor(qb, BQ, k), idesc_acc, (n | k) != 0);
-                    ptx::umma_commit(t_empty);
-                    ptx::umma_commit(&q_empty[st]);
+                    ptx::umma_commit(&t_empty[st]);
+                    ptx::umma_commit(&q_empty[qs]);
                     if (n == inner - 1) { ptx::umma_commit(acc_full); ptx::umma_commit(kv_empty); }
                 }
                 __syncwarp();
@@ -442,14 +488,17 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
         const int q4 = warp & 3;
         const int r = q4 * 32 + lane;                                  // key row inside the tile = TMEM lane
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
-        const int tid = threadIdx.x - 64;                              // 0..127
+        const int tid = threadIdx.x - 64;                              // 0..255
+        const int half = (warp - 2) >> 2;                              // which 32 of the 64 query columns / which half of hd
         int item_it = 0, n_it = 0;
         for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
-            int b, g, kt; decode(it, b, g, kt);
+            int b, g, kt, n0, n1; bool whole;
+            dkv_decode(a, it, rep, q_tiles64, k_tiles, b, g, kt, n0, n1, whole);
             const int kj = kt * BK + r;
-            for (int hh = 0; hh < rep; ++hh) {
-                const int h = g * rep + hh;
-                for (int qt = kt * (BK / BQ); qt < q_tiles64; ++qt, ++n_it) {
+            const int nq = q_tiles64 - 2 * kt;
+            {
+                for (int n = n0; n < n1; ++n, ++n_it) {
+                    const int h = g * rep + n / nq, qt = 2 * kt + n % nq;
                     // stage this query tile's lse / delta (read by every thread below)
                     float* lse_s = sLse + (n_it & 1) * BQ;
                     float* del_s = sDelta + (n_it & 1) * BQ;
@@ -458,27 +507,33 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                         lse_s[tid] = a.lse[o];
                         del_s[tid] = a.delta[o];
                     }
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                    ptx::mbar_wait(s_full, n_it & 1);
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    const int st = n_it & 1;
+                    ptx::mbar_wait(&s_full[st], (n_it >> 1) & 1);
+                    ptx::mbar_wait(&t_empty[st], ((n_it >> 1) & 1) ^ 1);   // dV/dK of iteration n-2 no longer read this buffer
                     ptx::tc_fence_after();
                     const bool diag = qt * BQ < kt * BK + BK;          // tile touches the diagonal: mask q < key
-                    const uint32_t ptb = ptx::smem_u32(sPT), dstb = ptx::smem_u32(sDST);
-#pragma unroll 1
-                    for (int c = 0; c < BQ; c += 32) {
+                    const uint32_t ptb = ptx::smem_u32(sPT + st * kTBytes), dstb = ptx::smem_u32(sDST + st * kTBytes);
+                    {
+                        const int c = half * 32;
                         uint32_t sv[32], dv[32];
-                        ptx::tmem_ld32(tmem + kTmS + lane_addr + c, sv);
-                        ptx::tmem_ld32(tmem + kTmDP + lane_addr + c, dv);
+                        ptx::tmem_ld32(tmem + st * 128 + lane_addr + c, sv);
+                        ptx::tmem_ld32(tmem + st * 128 + kTmDP + lane_addr + c, dv);
                         ptx::tmem_ld_wait();
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
-                            float p[8], ds[8];
+                            float p[8], ds[8], ls[8], dl[8];
+                            *reinterpret_cast<float4*>(ls) = *reinterpret_cast<const float4*>(lse_s + c + u * 8);
+                            *reinterpret_cast<float4*>(ls + 4) = *reinterpret_cast<const float4*>(lse_s + c + u * 8 + 4);
+                            *reinterpret_cast<float4*>(dl) = *reinterpret_cast<const float4*>(del_s + c + u * 8);
+                            *reinterpret_cast<float4*>(dl + 4) = *reinterpret_cast<const float4*>(del_s + c + u * 8 + 4);
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 const int col = c + u * 8 + i;
-                                float e = exp2f(__uint_as_float(sv[u * 8 + i]) * a.scale_log2 - lse_s[col]);
+                                float e = exp2f(fmaf(__uint_as_float(sv[u * 8 + i]), a.scale_log2, -ls[i]));
                                 if (diag && qt * BQ + col < kj) e = 0.f;
                                 p[i] = e;
-                                ds[i] = e * (__uint_as_float(dv[u * 8 + i]) - del_s[col]);
+                                ds[i] = e * (__uint_as_float(dv[u * 8 + i]) - dl[i]);
                             }
                             st_shared16(sw128_addr(ptb, BK, r, c + u * 8), pack8(p));
                             st_shared16(sw128_addr(dstb, BK, r, c + u * 8), pack8(ds));
@@ -487,7 +542,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     ptx::tc_fence_before();
                     ptx::fence_proxy_async();
                     __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(t_full);
+                    if (lane == 0) ptx::mbar_arrive(&t_full[st]);
                 }
             }
             // epilogue of the item: dV, dK (scaled, inverse-rotated) -> d(qkv)
@@ -495,11 +550,23 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             ptx::tc_fence_after();
             const int64_t trow = (int64_t)(b * a.S + kj) * a.ld_out;
 #pragma unroll 1
-            for (int c = 0; c < HD; c += 32) {
+            for (int c = half * (HD / 2); c < (half + 1) * (HD / 2); c += 32) {
                 uint32_t v[32], kk[32];
                 ptx::tmem_ld32(tmem + kTmDV + lane_addr + c, v);
                 ptx::tmem_ld32(tmem + kTmDK + lane_addr + c, kk);
                 ptx::tmem_ld_wait();
+                if (!whole) {   // a chunk of a longer item: raw fp32 partial sums for attn_dkv_reduce
+                    float* pv = a.partial + (((int64_t)it * 2 + 0) * BK + r) * HD + c;
+                    float* pk = a.partial + (((int64_t)it * 2 + 1) * BK + r) * HD + c;
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) {
+                        *reinterpret_cast<float4*>(pv + i) = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                                                                         __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+                        *reinterpret_cast<float4*>(pk + i) = make_float4(__uint_as_float(kk[i]), __uint_as_float(kk[i + 1]),
+                                                                         __uint_as_float(kk[i + 2]), __uint_as_float(kk[i + 3]));
+                    }
+                    continue;
+                }
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     float fv[8], fk[8];
@@ -523,6 +590,38 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     if (warp == 1) ptx::tmem_dealloc<512>(tmem);
 }
 
+// Fold the chunk partials of every (batch, kv head, key tile) that was split, in chunk order; scale and un-rotate dK.
+// Block = 8 key rows x (hd / 8) column groups, so a warp reads whole 128-byte lines of the partials.
+template <int HD>
+__global__ void __launch_bounds__(8 * (HD / 8))
+attn_dkv_reduce_kernel(const AttnArgs a) {
+    const int k_tiles = a.S / 128, q_tiles64 = a.S / 64, rep = a.H / a.KV;
+    const int rg = blockIdx.x % 16, item = blockIdx.x / 16;            // 16 groups of 8 rows per 128-key tile
+    const int kt = item % k_tiles, bg = item / k_tiles;
+    const int b = bg / a.KV, g = bg % a.KV;
+    const int r = rg * 8 + threadIdx.x / (HD / 8), d = (threadIdx.x % (HD / 8)) * 8;
+    int prefix = 0;
+    for (int k = 0; k < kt; ++k) prefix += (rep * (q_tiles64 - 2 * k) + a.chunk_len - 1) / a.chunk_len;
+    const int nc = (rep * (q_tiles64 - 2 * kt) + a.chunk_len - 1) / a.chunk_len;
+    if (nc == 1) return;                       // written directly by the main kernel
+    const int kj = kt * 128 + r;
+    const int64_t trow = (int64_t)(b * a.S + kj) * a.ld_out;
+    float fv[8] = {0, 0, 0, 0, 0, 0, 0, 0}, fk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int c = 0; c < nc; ++c) {
+        const int64_t u = (int64_t)(prefix + c) * (a.B * a.KV) + bg;
+        const float4* pv = reinterpret_cast<const float4*>(a.partial + ((u * 2 + 0) * 128 + r) * HD + d);
+        const float4* pk = reinterpret_cast<const float4*>(a.partial + ((u * 2 + 1) * 128 + r) * HD + d);
+        const float4 v0 = pv[0], v1 = pv[1], k0 = pk[0], k1 = pk[1];
+        fv[0] += v0.x; fv[1] += v0.y; fv[2] += v0.z; fv[3] += v0.w; fv[4] += v1.x; fv[5] += v1.y; fv[6] += v1.z; fv[7] += v1.w;
+        fk[0] += k0.x; fk[1] += k0.y; fk[2] += k0.z; fk[3] += k0.w; fk[4] += k1.x; fk[5] += k1.y; fk[6] += k1.z; fk[7] += k1.w;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) fk[i] *= a.scale;
+    unrope8(fk, a, kj, d, HD);
+    st8(a.out + trow + (a.H + a.KV + g) * HD + d, pack8(fv));
+    st8(a.out + trow + (a.H + g) * HD + d, pack8(fk));
+}
+
 // ================================================================================================= backward: dQ
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
@@ -530,25 +629,26 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                    const __grid_constant__ CUtensorMap tmDO, const AttnArgs a) {
     constexpr int BM = 128, BN = 64;                   // query tile (UMMA M), key tile (UMMA N)
     constexpr int kQBytes = BM * HD * 2, kKBytes = BN * HD * 2, kSBytes = BM * BN * 2;
-    constexpr int kTmS = 0, kTmDP = 64, kTmDQ = 128;
+    constexpr int kTmDP = 64, kTmDQ = 256;            // S / dP of buffer b at b*128 and b*128 + 64
+    constexpr int NK = 4;      // K / V stages: loads run ahead of the MMAs
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
     uint8_t* sDO = sQ + kQBytes;
-    uint8_t* sK = sDO + kQBytes;                       // 2 stages [BN x HD]
-    uint8_t* sV = sK + 2 * kKBytes;                    // 2 stages
-    uint8_t* sDS = sV + 2 * kKBytes;                   // dS [BM x BN]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + kSBytes);
+    uint8_t* sK = sDO + kQBytes;                       // NK stages [BN x HD]
+    uint8_t* sV = sK + NK * kKBytes;                   // NK stages
+    uint8_t* sDS = sV + NK * kKBytes;                  // dS [BM x BN], 2 buffers
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + 2 * kSBytes);
     uint64_t* q_full = bars;         // 1
     uint64_t* q_empty = bars + 1;    // 1
-    uint64_t* kv_full = bars + 2;    // 2
-    uint64_t* kv_empty = bars + 4;   // 2
-    uint64_t* s_full = bars + 6;     // 1
-    uint64_t* t_full = bars + 7;     // 1
-    uint64_t* t_empty = bars + 8;    // 1
-    uint64_t* acc_full = bars + 9;   // 1
-    uint64_t* acc_empty = bars + 10; // 1
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+    uint64_t* kv_full = bars + 2;    // NK
+    uint64_t* kv_empty = bars + 6;   // NK
+    uint64_t* s_full = bars + 10;    // 2
+    uint64_t* t_full = bars + 12;    // 2
+    uint64_t* t_empty = bars + 14;   // 2
+    uint64_t* acc_full = bars + 16;  // 1
+    uint64_t* acc_empty = bars + 17; // 1
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q_tiles = a.S / BM, rep = a.H / a.KV;
@@ -557,12 +657,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmQKV);
         ptx::mbar_init(q_full, 1); ptx::mbar_init(q_empty, 1);
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
-        ptx::mbar_init(s_full, 1); ptx::mbar_init(t_full, 4); ptx::mbar_init(t_empty, 1);
-        ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_empty, 4);
+        for (int i = 0; i < NK; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&t_full[i], 8); ptx::mbar_init(&t_empty[i], 1);
+        }
+        ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_empty, 8);
         ptx::fence_barrier_init();
     }
-    if (warp == 1) ptx::tmem_alloc<256>(tmem_slot);
+    if (warp == 1) ptx::tmem_alloc<512>(tmem_slot);
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -589,8 +691,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 }
                 const int nkv = (qt + 1) * (BM / BN);
                 for (int j = 0; j < nkv; ++j, ++kv_it) {
-                    const int st = kv_it & 1;
-                    ptx::mbar_wait(&kv_empty[st], ((kv_it >> 1) & 1) ^ 1);
+                    const int st = kv_it % NK;
+                    ptx::mbar_wait(&kv_empty[st], ((kv_it / NK) & 1) ^ 1);
                     ptx::mbar_arrive_expect_tx(&kv_full[st], 2 * kKBytes);
                     const int krow = b * a.S + j * BN;
 #pragma unroll
@@ -604,45 +706,50 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     } else if (warp == 1) {
         constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(BM, BN, false, false);
         constexpr uint32_t idesc_q = ptx::umma_idesc_bf16(BM, HD, false, true);    // dQ = dS K, B = K MN-major
-        int item_it = 0, kv_it = 0, n_it = 0;
+        int item_it = 0, n_it = 0;                                      // n_it: global key-tile counter
+        const uint32_t qa = ptx::smem_u32(sQ), doa = ptx::smem_u32(sDO);
+        auto issue_sdp = [&](int t) {                                   // S, dP of tile t -> TMEM buffer t & 1
+            const int st = t & 1, ks = t % NK;
+            ptx::mbar_wait(&kv_full[ks], (t / NK) & 1);
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+                const uint32_t kb = ptx::smem_u32(sK + ks * kKBytes), vb = ptx::smem_u32(sV + ks * kKBytes);
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    ptx::umma_bf16(tmem + st * 128, desc_kmajor(qa, BM, k), desc_kmajor(kb, BN, k), idesc_s, k != 0);
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    ptx::umma_bf16(tmem + st * 128 + kTmDP, desc_kmajor(doa, BM, k), desc_kmajor(vb, BN, k), idesc_s, k != 0);
+                ptx::umma_commit(&s_full[st]);
+            }
+            __syncwarp();
+        };
         for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
             int b, h, qt; decode(it, b, h, qt);
             ptx::mbar_wait(q_full, item_it & 1);
             ptx::mbar_wait(acc_empty, (item_it & 1) ^ 1);
             const int nkv = (qt + 1) * (BM / BN);
-            for (int j = 0; j < nkv; ++j, ++kv_it, ++n_it) {
-                const int st = kv_it & 1;
-                ptx::mbar_wait(&kv_full[st], (kv_it >> 1) & 1);
-                ptx::mbar_wait(t_empty, (n_it & 1) ^ 1);
-                ptx::tc_fence_after();
-                const uint32_t qa = ptx::smem_u32(sQ), doa = ptx::smem_u32(sDO);
-                const uint32_t kb = ptx::smem_u32(sK + st * kKBytes), vb = ptx::smem_u32(sV + st * kKBytes);
-                if (ptx::elect_one()) {
-#pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmS, desc_kmajor(qa, BM, k), desc_kmajor(kb, BN, k), idesc_s, k != 0);
-#pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmDP, desc_kmajor(doa, BM, k), desc_kmajor(vb, BN, k), idesc_s, k != 0);
-                    ptx::umma_commit(s_full);
-                }
-                __syncwarp();
-                ptx::mbar_wait(t_full, n_it & 1);
+            issue_sdp(n_it);
+            for (int j = 0; j < nkv; ++j, ++n_it) {
+                if (j + 1 < nkv) issue_sdp(n_it + 1);
+                const int st = n_it & 1;
+                ptx::mbar_wait(&t_full[st], (n_it >> 1) & 1);
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
-                    const uint32_t dsa = ptx::smem_u32(sDS);
+                    const int ks = n_it % NK;
+                    const uint32_t dsa = ptx::smem_u32(sDS + st * kSBytes), kb = ptx::smem_u32(sK + ks * kKBytes);
 #pragma unroll
                     for (int k = 0; k < BN / 16; ++k)
                         ptx::umma_bf16(tmem + kTmDQ, desc_kmajor(dsa, BM, k), desc_mnmajor(kb, BN, k), idesc_q, (j | k) != 0);
-                    ptx::umma_commit(t_empty);
-                    ptx::umma_commit(&kv_empty[st]);
+                    ptx::umma_commit(&t_empty[st]);
+                    ptx::umma_commit(&kv_empty[ks]);
                     if (j == nkv - 1) { ptx::umma_commit(acc_full); ptx::umma_commit(q_empty); }
                 }
                 __syncwarp();
             }
         }
     } else {
-        const int q4 = warp & 3;
+        const int q4 = warp & 3, half = (warp - 2) >> 2;
         const int r = q4 * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
         int item_it = 0, n_it = 0;
@@ -653,15 +760,17 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             const float lse = a.lse[so], delta = a.delta[so];
             const int nkv = (qt + 1) * (BM / BN);
             for (int j = 0; j < nkv; ++j, ++n_it) {
-                ptx::mbar_wait(s_full, n_it & 1);
+                const int st = n_it & 1;
+                ptx::mbar_wait(&s_full[st], (n_it >> 1) & 1);
+                ptx::mbar_wait(&t_empty[st], ((n_it >> 1) & 1) ^ 1);   // dQ MMA of tile n-2 no longer reads this dS buffer
                 ptx::tc_fence_after();
                 const bool diag = j * BN + BN > qt * BM;
-                const uint32_t dsb = ptx::smem_u32(sDS);
-#pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
+                const uint32_t dsb = ptx::smem_u32(sDS + st * kSBytes);
+                {
+                    const int c = half * 32;
                     uint32_t sv[32], dv[32];
-                    ptx::tmem_ld32(tmem + kTmS + lane_addr + c, sv);
-                    ptx::tmem_ld32(tmem + kTmDP + lane_addr + c, dv);
+                    ptx::tmem_ld32(tmem + st * 128 + lane_addr + c, sv);
+                    ptx::tmem_ld32(tmem + st * 128 + kTmDP + lane_addr + c, dv);
                     ptx::tmem_ld_wait();
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
@@ -679,13 +788,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 ptx::tc_fence_before();
                 ptx::fence_proxy_async();
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(t_full);
+                if (lane == 0) ptx::mbar_arrive(&t_full[st]);
             }
             ptx::mbar_wait(acc_full, item_it & 1);
             ptx::tc_fence_after();
             __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD;
 #pragma unroll 1
-            for (int c = 0; c < HD; c += 32) {
+            for (int c = half * (HD / 2); c < (half + 1) * (HD / 2); c += 32) {
                 uint32_t v[32];
                 ptx::tmem_ld32(tmem + kTmDQ + lane_addr + c, v);
                 ptx::tmem_ld_wait();
@@ -705,7 +814,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     }
     ptx::tc_fence_before();
     __syncthreads();
-    if (warp == 1) ptx::tmem_dealloc<256>(tmem);
+    if (warp == 1) ptx::tmem_dealloc<512>(tmem);
 }
 
 // ------------------------------------------------------------------------------------------------------- host
@@ -754,22 +863,42 @@ FTL_API int ftl_attn_fwd(const void* qkv, int64_t ld_qkv, void* out, int64_t ld_
     const int items = B * H * (S / 128);
     const int grid = items < kNumSMs ? items : kNumSMs;
     if (hd == 128) {
-        constexpr int smem = 128 * 128 * 2 * 6 + 1024 + 256;
+        constexpr int smem = 128 * 128 * 2 * 7 + 1024 + 128 + 1024;   // Q + 2 K + 2 V + 2 P = 224 KB, barriers, exchange
         static bool once = false; if (!once) { if ((e = set_smem(attn_fwd_kernel<128>, smem))) return e; once = true; }
         attn_fwd_kernel<128><<<grid, kAttnThreads, smem, stream>>>(tm, a);
     } else {
-        constexpr int smem = 128 * 64 * 2 * 5 + 128 * 128 * 2 + 1024 + 256;
+        constexpr int smem = 128 * 64 * 2 * 5 + 2 * 128 * 128 * 2 + 1024 + 128 + 1024;
         static bool once = false; if (!once) { if ((e = set_smem(attn_fwd_kernel<64>, smem))) return e; once = true; }
         attn_fwd_kernel<64><<<grid, kAttnThreads, smem, stream>>>(tm, a);
     }
     return (int)cudaGetLastError();
 }
 
+static void dkv_plan(int B, int S, int H, int KV, int* chunk_len, int* units) {
+    const int rep = H / KV, q64 = S / 64, kt_n = S / 128;
+    int64_t total = 0;
+    for (int k = 0; k < kt_n; ++k) total += (int64_t)rep * (q64 - 2 * k);
+    total *= (int64_t)B * KV;
+    int lc = (int)((total + 4 * kNumSMs - 1) / (4 * kNumSMs));
+    if (lc < 8) lc = 8;
+    int u = 0;
+    for (int k = 0; k < kt_n; ++k) u += (rep * (q64 - 2 * k) + lc - 1) / lc;
+    *chunk_len = lc;
+    *units = u * B * KV;
+}
+
+// bytes of fp32 scratch ftl_attn_bwd needs (partials of the split dK/dV items)
+FTL_API int64_t ftl_attn_bwd_scratch_bytes(int B, int S, int H, int KV, int hd) {
+    int lc, units;
+    dkv_plan(B, S, H, KV, &lc, &units);
+    return (int64_t)units * 2 * 128 * hd * 4;
+}
+
 // d_out: [B*S, H*hd] gradient of the attention output; out: the forward output; writes dq | dk | dv into dqkv
 // ([B*S, ld_qkv]) with the inverse RoPE applied to dq and dk when cos/sin are given.  delta: fp32 scratch [B, H, S].
 FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const void* d_out, int64_t ld_out, const float* lse,
-                         float* delta, void* dqkv, const float* cos_t, const float* sin_t, int B, int S, int H, int KV, int hd,
-                         cudaStream_t stream) {
+                         float* delta, void* dqkv, const float* cos_t, const float* sin_t, float* scratch, int B, int S, int H,
+                         int KV, int hd, cudaStream_t stream) {
     if (S % 128 || (hd != 64 && hd != 128) || H % KV || ld_qkv % 8 || ld_out % 8) return (int)cudaErrorInvalidValue;
     const int64_t T = (int64_t)B * S;
     CUtensorMap tq128, tq64, tdo128, tdo64;
@@ -789,10 +918,12 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
     a.out = (__nv_bfloat16*)dqkv; a.ld_out = ld_qkv; a.lse = const_cast<float*>(lse); a.delta = delta;
     a.B = B; a.S = S; a.H = H; a.KV = KV; a.ld_qkv = (int)ld_qkv;
     a.scale = 1.f / sqrtf((float)hd); a.scale_log2 = a.scale * kLog2e;
-    const int items_kv = B * KV * (S / 128), items_q = B * H * (S / 128);
+    dkv_plan(B, S, H, KV, &a.chunk_len, &a.units);
+    a.partial = scratch;
+    const int items_kv = a.units, items_q = B * H * (S / 128), items_red = B * KV * (S / 128);
     if (hd == 128) {
-        constexpr int smem_kv = 2 * 128 * 128 * 2 + 4 * 64 * 128 * 2 + 2 * 128 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
-        constexpr int smem_q = 2 * 128 * 128 * 2 + 4 * 64 * 128 * 2 + 128 * 64 * 2 + 1024 + 256;
+        constexpr int smem_kv = 2 * 128 * 128 * 2 + 6 * 64 * 128 * 2 + 4 * 128 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
+        constexpr int smem_q = 2 * 128 * 128 * 2 + 8 * 64 * 128 * 2 + 2 * 128 * 64 * 2 + 1024 + 256;
         static bool once = false;
         if (!once) {
             if ((e = set_smem(attn_bwd_dkv_kernel<128>, smem_kv))) return e;
@@ -801,10 +932,12 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
         }
         attn_bwd_dkv_kernel<128><<<items_kv < kNumSMs ? items_kv : kNumSMs, kAttnThreads, smem_kv, stream>>>(tq128, tq64, tdo64, a);
         FTL_LAUNCH_CHECK();
+        attn_dkv_reduce_kernel<128><<<items_red * 16, 128, 0, stream>>>(a);
+        FTL_LAUNCH_CHECK();
         attn_bwd_dq_kernel<128><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq128, tq64, tdo128, a);
     } else {
-        constexpr int smem_kv = 2 * 128 * 64 * 2 + 4 * 64 * 64 * 2 + 2 * 128 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
-        constexpr int smem_q = 2 * 128 * 64 * 2 + 4 * 64 * 64 * 2 + 128 * 64 * 2 + 1024 + 256;
+        constexpr int smem_kv = 2 * 128 * 64 * 2 + 6 * 64 * 64 * 2 + 4 * 128 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
+        constexpr int smem_q = 2 * 128 * 64 * 2 + 8 * 64 * 64 * 2 + 2 * 128 * 64 * 2 + 1024 + 256;
         static bool once = false;
         if (!once) {
             if ((e = set_smem(attn_bwd_dkv_kernel<64>, smem_kv))) return e;
@@ -812,6 +945,8 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
             once = true;
         }
         attn_bwd_dkv_kernel<64><<<items_kv < kNumSMs ? items_kv : kNumSMs, kAttnThreads, smem_kv, stream>>>(tq128, tq64, tdo64, a);
+        FTL_LAUNCH_CHECK();
+        attn_dkv_reduce_kernel<64><<<items_red * 16, 64, 0, stream>>>(a);
         FTL_LAUNCH_CHECK();
         attn_bwd_dq_kernel<64><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq128, tq64, tdo128, a);
     }

@@ -83,7 +83,8 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_fsdp_gather", [P, I64, P, I64, I, I, P, I, P])
     _sig(L, "ftl_adamw_shard", [P, P, P, P, I64, P, P, P, P, I, P])
     _sig(L, "ftl_attn_fwd", [P, I64, P, I64, P, I, I, I, I, I, P])
-    _sig(L, "ftl_attn_bwd", [P, I64, P, P, I64, P, P, P, P, P, I, I, I, I, I, P])
+    _sig(L, "ftl_attn_bwd", [P, I64, P, P, I64, P, P, P, P, P, P, I, I, I, I, I, P])
+    _sig(L, "ftl_attn_bwd_scratch_bytes", [I, I, I, I, I], c_int64)
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -399,11 +400,25 @@ def attn_fwd(qkv, out, lse, B, S, H, KV, hd):
     return out
 
 
-def attn_bwd(qkv, out, d_out, lse, delta, dqkv, B, S, H, KV, hd, cos=None, sin=None):
+_ATTN_SCRATCH = {}
+
+
+def attn_bwd_scratch(B, S, H, KV, hd, device) -> torch.Tensor:
+    """fp32 work area of the backward (chunk partials of dK/dV); cached per shape."""
+    key = (B, S, H, KV, hd, str(device))
+    if key not in _ATTN_SCRATCH:
+        n = lib().ftl_attn_bwd_scratch_bytes(B, S, H, KV, hd) // 4
+        _ATTN_SCRATCH[key] = torch.empty(max(n, 1), dtype=torch.float32, device=device)
+    return _ATTN_SCRATCH[key]
+
+
+def attn_bwd(qkv, out, d_out, lse, delta, dqkv, B, S, H, KV, hd, cos=None, sin=None, scratch=None):
     """Deterministic backward: writes dq | dk | dv into dqkv ([B*S, (H+2KV)*hd]); with cos/sin the inverse rotary
     embedding is applied to dq and dk, so dqkv is the gradient of the un-rotated projection."""
     _mat(qkv), _mat(out), _mat(d_out), _mat(dqkv)
     assert out.stride(0) == d_out.stride(0) and dqkv.stride(0) == qkv.stride(0) and delta.numel() == B * H * S
+    if scratch is None:
+        scratch = attn_bwd_scratch(B, S, H, KV, hd, qkv.device)
     _check(lib().ftl_attn_bwd(_ptr(qkv), qkv.stride(0), _ptr(out), _ptr(d_out), out.stride(0), _ptr(lse), _ptr(delta),
-                              _ptr(dqkv), _ptr(cos), _ptr(sin), B, S, H, KV, hd, _stream()), "ftl_attn_bwd", 3)
+                              _ptr(dqkv), _ptr(cos), _ptr(sin), _ptr(scratch), B, S, H, KV, hd, _stream()), "ftl_attn_bwd", 4)
     return dqkv
