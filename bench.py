@@ -170,6 +170,8 @@ def run_ours(a) -> dict:
                    "global_batch": a.batch * env.world_size, "seq_len": a.seq,
                    "parallelism": ("single" if env.world_size == 1 else f"{trainer.parallel}{env.world_size}"),
                    "optimizer": "AdamW fused, bf16 states, grad clip 1.0", "params": cfg.num_params(),
+                   "kernels": {"gemm": os.environ.get("FTL_GEMM", "tc") + " (tc = own tcgen05 CTA-pair kernel)",
+                               "attention": os.environ.get("FTL_ATTN", "tc") + " (tc = own tcgen05 flash attention, deterministic)"},
                    "l2": "no flush: each step streams >64 GB of weights/grads/moments, far larger than the 126 MB L2"},
         "clocks": sampler.summary(), "gpu_launches": int(gpu_launches),
         "loss": round(float(loss_dev), 4),

@@ -48,13 +48,28 @@ __device__ __forceinline__ void st_shared16(uint32_t addr, const bf16x8& v) {
     asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w) : "memory");
 }
 
-// K-major operand tile [rows x kdim] (kdim contiguous): descriptor for the k16-th UMMA step.
-__device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, int rows, int k16) {
-    return ptx::umma_smem_desc(base + (k16 >> 2) * rows * 128 + (k16 & 3) * 32, 0, 1024);
+// The MMA warp is ONE thread issuing every tcgen05.mma of the CTA; a 128x64x16 UMMA occupies the tensor pipe for only
+// ~32 cycles, so building each 64-bit descriptor from scratch (~15 dependent integer ops) made instruction issue, not
+// the tensor pipe, the limiter of these kernels.  Descriptors are therefore built once per operand tile (k16 = 0) and
+// stepped by adding a compile-time constant to the 14-bit start-address field (addresses are < 256 KB: no carry).
+// K-major operand tile [rows x kdim] (kdim contiguous, 64-column chunks of rows*128 bytes): step k16 -> +32 B inside a
+// chunk, next chunk every 4 steps.
+__device__ __forceinline__ uint64_t desc_kmajor0(uint32_t base) { return ptx::umma_smem_desc(base, 0, 1024); }
+__device__ __forceinline__ uint64_t desc_kmajor_step(uint64_t d0, int rows, int k16) {
+    return d0 + (uint64_t)(((k16 >> 2) * rows * 128 + (k16 & 3) * 32) >> 4);
 }
 // MN-major operand: tile stored [krows x mn] (mn contiguous, chunked by 64): step k16 covers rows 16*k16..+15.
-__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int krows, int k16) {
-    return ptx::umma_smem_desc(base + k16 * 16 * 128, krows * 128, 1024);
+__device__ __forceinline__ uint64_t desc_mnmajor0(uint32_t base, int krows) { return ptx::umma_smem_desc(base, krows * 128, 1024); }
+__device__ __forceinline__ uint64_t desc_mnmajor_step(uint64_t d0, int k16) { return d0 + (uint64_t)((k16 * 16 * 128) >> 4); }
+// D[tmem] (+)= A * B over KSTEPS UMMA steps; A K-major with ROWS_A rows, B either K-major (ROWS_B rows) or MN-major.
+template <int KSTEPS, int ROWS_A, int ROWS_B, bool B_MN>
+__device__ __forceinline__ void umma_tile(uint32_t tmem_d, uint32_t a_base, uint32_t b_base, uint32_t idesc, bool accumulate) {
+    const uint64_t da = desc_kmajor0(a_base);
+    const uint64_t db = B_MN ? desc_mnmajor0(b_base, ROWS_B) : desc_kmajor0(b_base);
+#pragma unroll
+    for (int k = 0; k < KSTEPS; ++k)
+        ptx::umma_bf16(tmem_d, desc_kmajor_step(da, ROWS_A, k), B_MN ? desc_mnmajor_step(db, k) : desc_kmajor_step(db, ROWS_B, k),
+                       idesc, (accumulate || k != 0) ? 1u : 0u);
 }
 
 struct AttnArgs {
@@ -184,10 +199,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 ptx::mbar_wait(&kv_full[st], (t >> 1) & 1);
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
-                    const uint32_t qa = ptx::smem_u32(sQ), kb = ptx::smem_u32(sK + st * kKBytes);
-#pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)
-                        ptx::umma_bf16(tmem + st * BN, desc_kmajor(qa, BM, k), desc_kmajor(kb, BN, k), idesc_s, k != 0);
+                    umma_tile<HD / 16, BM, BN, false>(tmem + st * BN, ptx::smem_u32(sQ), ptx::smem_u32(sK + st * kKBytes), idesc_s, false);
                     ptx::umma_commit(&s_full[st]);
                 }
                 __syncwarp();
@@ -200,10 +212,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 ptx::mbar_wait(&o_empty[st], ph ^ 1);                 // O buffer st (tile t-2) has been folded
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
-                    const uint32_t pa = ptx::smem_u32(sP + st * kPBytes), vb = ptx::smem_u32(sV + st * kKBytes);
-#pragma unroll
-                    for (int k = 0; k < BN / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmemO + st * BN, desc_kmajor(pa, BM, k), desc_mnmajor(vb, BN, k), idesc_o, k != 0);
+                    umma_tile<BN / 16, BM, BN, true>(tmem + kTmemO + st * BN, ptx::smem_u32(sP + st * kPBytes),
+                                                     ptx::smem_u32(sV + st * kKBytes), idesc_o, false);
                     ptx::umma_commit(&o_full[st]);
                     ptx::umma_commit(&kv_empty[st]);
                     if (j == nkv - 1) ptx::umma_commit(q_empty);
@@ -419,8 +429,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     ptx::tma_load_2d(sV + c * BK * 128, &tmQKV, kv_full, (a.H + a.KV + g) * HD + c * 64, krow);
                 }
                 const int nq = q_tiles64 - 2 * kt;
+                int hh = n0 / nq, qo = n0 % nq;
                 for (int n = n0; n < n1; ++n, ++q_it) {
-                    const int h = g * rep + n / nq, qt = 2 * kt + n % nq;
+                    const int h = g * rep + hh, qt = 2 * kt + qo;
+                    if (++qo == nq) { qo = 0; ++hh; }
                     const int st = q_it % NQ;
                     ptx::mbar_wait(&q_empty[st], ((q_it / NQ) & 1) ^ 1);
                     ptx::mbar_arrive_expect_tx(&q_full[st], 2 * kQBytes);
@@ -445,12 +457,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             ptx::tc_fence_after();
             if (ptx::elect_one()) {
                 const uint32_t qb = ptx::smem_u32(sQ + qs * kQBytes), dob = ptx::smem_u32(sDO + qs * kQBytes);
-#pragma unroll
-                for (int k = 0; k < HD / 16; ++k)
-                    ptx::umma_bf16(tmem + st * 128, desc_kmajor(ka, BK, k), desc_kmajor(qb, BQ, k), idesc_st, k != 0);
-#pragma unroll
-                for (int k = 0; k < HD / 16; ++k)
-                    ptx::umma_bf16(tmem + st * 128 + kTmDP, desc_kmajor(va, BK, k), desc_kmajor(dob, BQ, k), idesc_st, k != 0);
+                umma_tile<HD / 16, BK, BQ, false>(tmem + st * 128, ka, qb, idesc_st, false);
+                umma_tile<HD / 16, BK, BQ, false>(tmem + st * 128 + kTmDP, va, dob, idesc_st, false);
                 ptx::umma_commit(&s_full[st]);
             }
             __syncwarp();
@@ -471,12 +479,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     const int qs = n_it % NQ;
                     const uint32_t qb = ptx::smem_u32(sQ + qs * kQBytes), dob = ptx::smem_u32(sDO + qs * kQBytes);
                     const uint32_t pt = ptx::smem_u32(sPT + st * kTBytes), dst = ptx::smem_u32(sDST + st * kTBytes);
-#pragma unroll
-                    for (int k = 0; k < BQ / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmDV, desc_kmajor(pt, BK, k), desc_mnmajor(dob, BQ, k), idesc_acc, (n | k) != 0);
-#pragma unroll
-                    for (int k = 0; k < BQ / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmDK, desc_kmajor(dst, BK, k), desc_mnmajor(qb, BQ, k), idesc_acc, (n | k) != 0);
+                    umma_tile<BQ / 16, BK, BQ, true>(tmem + kTmDV, pt, dob, idesc_acc, n != 0);
+                    umma_tile<BQ / 16, BK, BQ, true>(tmem + kTmDK, dst, qb, idesc_acc, n != 0);
                     ptx::umma_commit(&t_empty[st]);
                     ptx::umma_commit(&q_empty[qs]);
                     if (n == inner - 1) { ptx::umma_commit(acc_full); ptx::umma_commit(kv_empty); }
@@ -497,15 +501,23 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             const int kj = kt * BK + r;
             const int nq = q_tiles64 - 2 * kt;
             {
+                // lse / delta of the NEXT iteration are fetched into registers while this one computes, so the
+                // global-load latency is off the critical path of the staging barrier
+                int hh = n0 / nq, qo = n0 % nq;                         // head within the group, query tile offset
+                float lse_r = 0.f, del_r = 0.f;
+                if (tid < BQ) {
+                    const int64_t o = ((int64_t)b * a.H + g * rep + hh) * a.S + (2 * kt + qo) * BQ + tid;
+                    lse_r = a.lse[o]; del_r = a.delta[o];
+                }
                 for (int n = n0; n < n1; ++n, ++n_it) {
-                    const int h = g * rep + n / nq, qt = 2 * kt + n % nq;
-                    // stage this query tile's lse / delta (read by every thread below)
+                    const int qt = 2 * kt + qo;
                     float* lse_s = sLse + (n_it & 1) * BQ;
                     float* del_s = sDelta + (n_it & 1) * BQ;
-                    if (tid < BQ) {
-                        const int64_t o = ((int64_t)b * a.H + h) * a.S + qt * BQ + tid;
-                        lse_s[tid] = a.lse[o];
-                        del_s[tid] = a.delta[o];
+                    if (tid < BQ) { lse_s[tid] = lse_r; del_s[tid] = del_r; }
+                    if (++qo == nq) { qo = 0; ++hh; }
+                    if (tid < BQ && n + 1 < n1) {
+                        const int64_t o = ((int64_t)b * a.H + g * rep + hh) * a.S + (2 * kt + qo) * BQ + tid;
+                        lse_r = a.lse[o]; del_r = a.delta[o];
                     }
                     asm volatile("bar.sync 1, 256;" ::: "memory");
                     const int st = n_it & 1;
@@ -714,12 +726,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             ptx::tc_fence_after();
             if (ptx::elect_one()) {
                 const uint32_t kb = ptx::smem_u32(sK + ks * kKBytes), vb = ptx::smem_u32(sV + ks * kKBytes);
-#pragma unroll
-                for (int k = 0; k < HD / 16; ++k)
-                    ptx::umma_bf16(tmem + st * 128, desc_kmajor(qa, BM, k), desc_kmajor(kb, BN, k), idesc_s, k != 0);
-#pragma unroll
-                for (int k = 0; k < HD / 16; ++k)
-                    ptx::umma_bf16(tmem + st * 128 + kTmDP, desc_kmajor(doa, BM, k), desc_kmajor(vb, BN, k), idesc_s, k != 0);
+                umma_tile<HD / 16, BM, BN, false>(tmem + st * 128, qa, kb, idesc_s, false);
+                umma_tile<HD / 16, BM, BN, false>(tmem + st * 128 + kTmDP, doa, vb, idesc_s, false);
                 ptx::umma_commit(&s_full[st]);
             }
             __syncwarp();
@@ -738,9 +746,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 if (ptx::elect_one()) {
                     const int ks = n_it % NK;
                     const uint32_t dsa = ptx::smem_u32(sDS + st * kSBytes), kb = ptx::smem_u32(sK + ks * kKBytes);
-#pragma unroll
-                    for (int k = 0; k < BN / 16; ++k)
-                        ptx::umma_bf16(tmem + kTmDQ, desc_kmajor(dsa, BM, k), desc_mnmajor(kb, BN, k), idesc_q, (j | k) != 0);
+                    umma_tile<BN / 16, BM, BN, true>(tmem + kTmDQ, dsa, kb, idesc_q, j != 0);
                     ptx::umma_commit(&t_empty[st]);
                     ptx::umma_commit(&kv_empty[ks]);
                     if (j == nkv - 1) { ptx::umma_commit(acc_full); ptx::umma_commit(q_empty); }

@@ -312,16 +312,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (ptx::elect_one()) {
                     const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes);
                     const uint32_t sb = sa + kABytes;
+                    // one UMMA consumes 16 reduction elements: 32 B inside the swizzle row (K-major) or 16 rows of
+                    // 128 B (MN-major).  The descriptor is built once per stage and stepped by adding a constant to
+                    // its start-address field: the single issuing thread must not spend ~30 integer ops per UMMA.
+                    const uint64_t da0 = kAMn ? ptx::umma_smem_desc(sa, kLboMn, kSbo) : ptx::umma_smem_desc(sa, 0, kSbo);
+                    const uint64_t db0 = kBMn ? ptx::umma_smem_desc(sb, kLboMn, kSbo) : ptx::umma_smem_desc(sb, 0, kSbo);
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k) {
-                        // one UMMA consumes 16 reduction elements: 32 B inside the swizzle row (K-major) or
-                        // 16 rows of 128 B (MN-major)
-                        const uint64_t da = kAMn ? ptx::umma_smem_desc(sa + k * 16 * 128, kLboMn, kSbo)
-                                                 : ptx::umma_smem_desc(sa + k * 32, 0, kSbo);
-                        const uint64_t db = kBMn ? ptx::umma_smem_desc(sb + k * 16 * 128, kLboMn, kSbo)
-                                                 : ptx::umma_smem_desc(sb + k * 32, 0, kSbo);
-                        ptx::umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0);
-                    }
+                    for (int k = 0; k < BK / 16; ++k)
+                        ptx::umma_bf16(tmem_d, da0 + (uint64_t)((kAMn ? k * 16 * 128 : k * 32) >> 4),
+                                       db0 + (uint64_t)((kBMn ? k * 16 * 128 : k * 32) >> 4), idesc, (kb | k) != 0);
                     // free the smem slot when the MMAs retire — in every CTA of the cluster, because the peers'
                     // multicast writes land in this CTA's slot too
                     if (kCluster == 1) ptx::umma_commit(&empty[stage]);
@@ -487,14 +486,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     if (ptx::elect_one()) {
                         const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes2);
                         const uint32_t sb = sa + kABytes;
+                        const uint64_t da0 = kAMn ? ptx::umma_smem_desc(sa, kLboMn, kSbo) : ptx::umma_smem_desc(sa, 0, kSbo);
+                        const uint64_t db0 = kBMn ? ptx::umma_smem_desc(sb, kLboMn, kSbo) : ptx::umma_smem_desc(sb, 0, kSbo);
 #pragma unroll
-                        for (int k = 0; k < BK / 16; ++k) {
-                            const uint64_t da = kAMn ? ptx::umma_smem_desc(sa + k * 16 * 128, kLboMn, kSbo)
-                                                     : ptx::umma_smem_desc(sa + k * 32, 0, kSbo);
-                            const uint64_t db = kBMn ? ptx::umma_smem_desc(sb + k * 16 * 128, kLboMn, kSbo)
-                                                     : ptx::umma_smem_desc(sb + k * 32, 0, kSbo);
-                            ptx::umma_bf16_2sm(tmem_d, da, db, idesc, (kb | k) != 0);
-                        }
+                        for (int k = 0; k < BK / 16; ++k)
+                            ptx::umma_bf16_2sm(tmem_d, da0 + (uint64_t)((kAMn ? k * 16 * 128 : k * 32) >> 4),
+                                               db0 + (uint64_t)((kBMn ? k * 16 * 128 : k * 32) >> 4), idesc, (kb | k) != 0);
                         ptx::umma_commit_2sm(&empty[stage], 3);
                         if (kb == num_kb - 1) ptx::umma_commit_2sm(&acc_full[acc], 3);
                     }

@@ -418,8 +418,8 @@ class NativeTrainer:
         # Bitwise-reproducible steps are part of the contract (kill/resume chains must replay exactly).  Everything in
         # csrc/ is deterministic by construction (fixed reduction orders, no float atomics); the one library op left
         # on the path, SDPA's backward, accumulates dQ with atomics at long sequence lengths unless told otherwise.
-        if os.environ.get("FTL_DETERMINISTIC", "1") == "1":
-            torch.use_deterministic_algorithms(True, warn_only=True)
+        if os.environ.get("FTL_ATTN", "tc") == "lib" and os.environ.get("FTL_DETERMINISTIC", "1") == "1":
+            torch.use_deterministic_algorithms(True, warn_only=True)   # only the library attention path needs it
         self.cfg, self.env, self.device = cfg, env, env.device
         self.parallel = parallel
         self.grad_max_norm, self.clip_mode = float(grad_max_norm), clip_mode
