@@ -107,6 +107,16 @@ __device__ __forceinline__ void dkv_decode(const AttnArgs& a, int u, int rep, in
     }
 }
 
+// D[tmem] (+)= A[tmem, bf16 pairs: 8 columns per UMMA step] * B[smem]
+template <int KSTEPS, int ROWS_B, bool B_MN>
+__device__ __forceinline__ void umma_tile_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_base, uint32_t idesc, bool accumulate) {
+    const uint64_t db = B_MN ? desc_mnmajor0(b_base, ROWS_B) : desc_kmajor0(b_base);
+#pragma unroll
+    for (int k = 0; k < KSTEPS; ++k)
+        ptx::umma_bf16_ts(tmem_d, tmem_a + k * 8, B_MN ? desc_mnmajor_step(db, k) : desc_kmajor_step(db, ROWS_B, k), idesc,
+                          (accumulate || k != 0) ? 1u : 0u);
+}
+
 // ================================================================================================= forward
 // Software pipeline (per CTA): the MMA warp issues S(j+1) as soon as K(j+1) has landed, i.e. while the math threads
 // are still in the softmax of tile j; P and the O tile are double-buffered, and the math threads fold O(j-1) into
@@ -115,25 +125,25 @@ template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
     constexpr int BM = 128, BN = 128;
-    constexpr int kQBytes = BM * HD * 2, kKBytes = BN * HD * 2, kPBytes = BM * BN * 2;
+    constexpr int kQBytes = BM * HD * 2, kKBytes = BN * HD * 2;
+    constexpr int NKV = 3;                            // K/V stages (P lives in TMEM, which freed the room for a third)
     constexpr int kTmemO = 2 * BN;                    // columns: S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512)
-    extern __shared__ uint8_t smem_raw[];
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
-    uint8_t* sK = sQ + kQBytes;                       // 2 stages
-    uint8_t* sV = sK + 2 * kKBytes;                   // 2 stages
-    uint8_t* sP = sV + 2 * kKBytes;                   // 2 buffers
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kPBytes);
-    float* sMax = reinterpret_cast<float*>(bars + 16);   // [2][BM] row-max / row-sum exchange between the column halves
+    uint8_t* sK = sQ + kQBytes;                       // NKV stages
+    uint8_t* sV = sK + NKV * kKBytes;                 // NKV stages
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + NKV * kKBytes);
+    float* sMax = reinterpret_cast<float*>(bars + 20);   // [2][2][BM] row-max / row-sum exchange between the column halves
     uint64_t* q_full = bars;          // 1
     uint64_t* q_empty = bars + 1;     // 1
-    uint64_t* kv_full = bars + 2;     // 2
-    uint64_t* kv_empty = bars + 4;    // 2
-    uint64_t* s_full = bars + 6;      // 2
-    uint64_t* p_full = bars + 8;      // 2
-    uint64_t* o_full = bars + 10;     // 2
-    uint64_t* o_empty = bars + 12;    // 2
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+    uint64_t* kv_full = bars + 2;     // NKV (<= 4)
+    uint64_t* kv_empty = bars + 6;    // NKV
+    uint64_t* s_full = bars + 10;     // 2
+    uint64_t* p_full = bars + 12;     // 2
+    uint64_t* o_full = bars + 14;     // 2
+    uint64_t* o_empty = bars + 16;    // 2
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q_tiles = a.S / BM;
@@ -143,8 +153,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmQKV);
         ptx::mbar_init(q_full, 1); ptx::mbar_init(q_empty, 1);
+        for (int i = 0; i < NKV; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
         for (int i = 0; i < 2; ++i) {
-            ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); ptx::mbar_init(&s_full[i], 1);
+            ptx::mbar_init(&s_full[i], 1);
             ptx::mbar_init(&p_full[i], 8); ptx::mbar_init(&o_full[i], 1); ptx::mbar_init(&o_empty[i], 8);
         }
         ptx::fence_barrier_init();
@@ -174,8 +185,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
 #pragma unroll
                 for (int c = 0; c < HD / 64; ++c) ptx::tma_load_2d(sQ + c * BM * 128, &tmQKV, q_full, h * HD + c * 64, row0);
                 for (int j = 0; j <= qt; ++j, ++kv_it) {
-                    const int st = kv_it & 1;
-                    ptx::mbar_wait(&kv_empty[st], ((kv_it >> 1) & 1) ^ 1);
+                    const int st = kv_it % NKV;
+                    ptx::mbar_wait(&kv_empty[st], ((kv_it / NKV) & 1) ^ 1);
                     ptx::mbar_arrive_expect_tx(&kv_full[st], 2 * kKBytes);
                     const int krow = b * a.S + j * BN;
 #pragma unroll
@@ -195,11 +206,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
             ptx::mbar_wait(q_full, q_it & 1);
             const int nkv = qt + 1;
             auto issue_s = [&](int t) {                                            // scores of global tile t
-                const int st = t & 1;
-                ptx::mbar_wait(&kv_full[st], (t >> 1) & 1);
+                const int st = t & 1, ks = t % NKV;
+                ptx::mbar_wait(&kv_full[ks], (t / NKV) & 1);
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
-                    umma_tile<HD / 16, BM, BN, false>(tmem + st * BN, ptx::smem_u32(sQ), ptx::smem_u32(sK + st * kKBytes), idesc_s, false);
+                    umma_tile<HD / 16, BM, BN, false>(tmem + st * BN, ptx::smem_u32(sQ), ptx::smem_u32(sK + ks * kKBytes), idesc_s, false);
                     ptx::umma_commit(&s_full[st]);
                 }
                 __syncwarp();
@@ -207,15 +218,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
             issue_s(t_it);
             for (int j = 0; j < nkv; ++j, ++t_it) {
                 if (j + 1 < nkv) issue_s(t_it + 1);                   // next scores while the softmax of this tile runs
-                const int st = t_it & 1, ph = (t_it >> 1) & 1;
+                const int st = t_it & 1, ph = (t_it >> 1) & 1, ks = t_it % NKV;
                 ptx::mbar_wait(&p_full[st], ph);                      // P(t) is in smem, S(t) has been read
                 ptx::mbar_wait(&o_empty[st], ph ^ 1);                 // O buffer st (tile t-2) has been folded
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
-                    umma_tile<BN / 16, BM, BN, true>(tmem + kTmemO + st * BN, ptx::smem_u32(sP + st * kPBytes),
-                                                     ptx::smem_u32(sV + st * kKBytes), idesc_o, false);
+                    // A = P, written by the math threads over the first 64 columns of the score buffer it came from:
+                    // only V is fetched from shared memory, which halves the operand traffic of this MMA
+                    umma_tile_ts<BN / 16, BN, true>(tmem + kTmemO + st * BN, tmem + st * BN, ptx::smem_u32(sV + ks * kKBytes),
+                                                    idesc_o, false);
                     ptx::umma_commit(&o_full[st]);
-                    ptx::umma_commit(&kv_empty[st]);
+                    ptx::umma_commit(&kv_empty[ks]);
                     if (j == nkv - 1) ptx::umma_commit(q_empty);
                 }
                 __syncwarp();
@@ -239,14 +252,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 const int st = t & 1;
                 ptx::mbar_wait(&o_full[st], (t >> 1) & 1);
                 ptx::tc_fence_after();
+                uint32_t v[OW];
 #pragma unroll
-                for (int c = 0; c < OW; c += 32) {
-                    uint32_t v[32];
-                    ptx::tmem_ld32(tmem + kTmemO + st * BN + lane_addr + d0 + c, v);
-                    ptx::tmem_ld_wait();
+                for (int c = 0; c < OW; c += 32)
+                    ptx::tmem_ld32(tmem + kTmemO + st * BN + lane_addr + d0 + c, *reinterpret_cast<uint32_t(*)[32]>(&v[c]));
+                ptx::tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) acc[c + i] = fmaf(acc[c + i], alpha, __uint_as_float(v[i]));
-                }
+                for (int i = 0; i < OW; ++i) acc[i] = fmaf(acc[i], alpha, __uint_as_float(v[i]));
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&o_empty[st]);
@@ -272,30 +284,30 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                     for (int i = 0; i < CW; ++i) if (i <= lim) mx = fmaxf(mx, __uint_as_float(v[i]));
                 }
                 // row maximum = max over the two halves: exchange through shared memory
-                sMax[half * BM + r] = mx;
+                float* xch = sMax + (t_it & 1) * 2 * BM;                 // double-buffered: one barrier per tile
+                xch[half * BM + r] = mx;
                 asm volatile("bar.sync 1, 256;" ::: "memory");
-                mx = fmaxf(mx, sMax[(half ^ 1) * BM + r]);
-                asm volatile("bar.sync 1, 256;" ::: "memory");          // all reads done before the next tile's writes
+                mx = fmaxf(mx, xch[(half ^ 1) * BM + r]);
                 const float m_new = fmaxf(m, mx * a.scale_log2);
                 const float alpha = exp2f(m - m_new);                   // m = -inf on the first tile -> 0
                 float sum = 0.f;
-                const uint32_t pbase = ptx::smem_u32(sP + st * kPBytes);
+                uint32_t pk[CW / 2];                                    // this thread's P values, two bf16 per register
 #pragma unroll
-                for (int u = 0; u < CW / 8; ++u) {
-                    float p[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        float e = exp2f(fmaf(__uint_as_float(v[u * 8 + i]), a.scale_log2, -m_new));
-                        if (diag && u * 8 + i > lim) e = 0.f;
-                        p[i] = e;
-                        sum += e;
-                    }
-                    st_shared16(sw128_addr(pbase, BM, r, c0 + u * 8), pack8(p));
+                for (int i = 0; i < CW; i += 2) {
+                    float e0 = exp2f(fmaf(__uint_as_float(v[i]), a.scale_log2, -m_new));
+                    float e1 = exp2f(fmaf(__uint_as_float(v[i + 1]), a.scale_log2, -m_new));
+                    if (diag && i > lim) e0 = 0.f;
+                    if (diag && i + 1 > lim) e1 = 0.f;
+                    sum += e0 + e1;
+                    pk[i >> 1] = ptx::pack_bf16x2(e0, e1);
                 }
+                // P overwrites the score buffer in place (both column halves loaded their scores before the exchange
+                // barrier above): columns [c0/2, c0/2 + 32) of this thread's TMEM lane
+                ptx::tmem_st32(tmem + st * BN + lane_addr + (c0 >> 1), pk);
+                ptx::tmem_st_wait();
                 l = fmaf(l, alpha, sum);                                // partial over this thread's columns
                 m = m_new;
                 ptx::tc_fence_before();
-                ptx::fence_proxy_async();                               // generic-proxy smem writes -> UMMA (async proxy)
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&p_full[st]);
                 if (j > 0) fold(t_it - 1, alpha_prev);                  // runs while the tensor core does P V of this tile
@@ -303,9 +315,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
             }
             fold(t_it - 1, alpha_prev);
             // finalize: the two halves add their partial row sums, then O / l and the lse
-            sMax[half * BM + r] = l;
+            float* xch = sMax + (t_it & 1) * 2 * BM;                     // the buffer the next tile would use: free
+            xch[half * BM + r] = l;
             asm volatile("bar.sync 1, 256;" ::: "memory");
-            l += sMax[(half ^ 1) * BM + r];
+            l += xch[(half ^ 1) * BM + r];
             const float inv = 1.f / l;
             __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD + d0;
 #pragma unroll
@@ -369,7 +382,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     constexpr int kKBytes = BK * HD * 2, kQBytes = BQ * HD * 2, kTBytes = BK * BQ * 2;
     constexpr int kTmDP = 64, kTmDV = 256, kTmDK = 256 + HD;   // S / dP of buffer b at b*128 and b*128 + 64
     constexpr int NQ = 3;      // Q / dO stages: the TMA loads run two iterations ahead of the MMAs that consume them
-    extern __shared__ uint8_t smem_raw[];
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem;
     uint8_t* sV = sK + kKBytes;
@@ -643,7 +656,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     constexpr int kQBytes = BM * HD * 2, kKBytes = BN * HD * 2, kSBytes = BM * BN * 2;
     constexpr int kTmDP = 64, kTmDQ = 256;            // S / dP of buffer b at b*128 and b*128 + 64
     constexpr int NK = 4;      // K / V stages: loads run ahead of the MMAs
-    extern __shared__ uint8_t smem_raw[];
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem;
     uint8_t* sDO = sQ + kQBytes;
@@ -869,11 +882,11 @@ FTL_API int ftl_attn_fwd(const void* qkv, int64_t ld_qkv, void* out, int64_t ld_
     const int items = B * H * (S / 128);
     const int grid = items < kNumSMs ? items : kNumSMs;
     if (hd == 128) {
-        constexpr int smem = 128 * 128 * 2 * 7 + 1024 + 128 + 1024;   // Q + 2 K + 2 V + 2 P = 224 KB, barriers, exchange
+        constexpr int smem = 128 * 128 * 2 * 7 + 160 + 2048 + 512;   // Q + 3 x (K, V) = 224 KB, barriers, exchange (base is 1024-aligned)
         static bool once = false; if (!once) { if ((e = set_smem(attn_fwd_kernel<128>, smem))) return e; once = true; }
         attn_fwd_kernel<128><<<grid, kAttnThreads, smem, stream>>>(tm, a);
     } else {
-        constexpr int smem = 128 * 64 * 2 * 5 + 2 * 128 * 128 * 2 + 1024 + 128 + 1024;
+        constexpr int smem = 128 * 64 * 2 * 7 + 160 + 2048 + 512;
         static bool once = false; if (!once) { if ((e = set_smem(attn_fwd_kernel<64>, smem))) return e; once = true; }
         attn_fwd_kernel<64><<<grid, kAttnThreads, smem, stream>>>(tm, a);
     }
