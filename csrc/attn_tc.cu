@@ -25,8 +25,10 @@
 #include <cuda_bf16.h>
 #include <cudaTypedefs.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "common/ptx.cuh"
 #include "common/util.cuh"
@@ -116,6 +118,15 @@ __device__ __forceinline__ void umma_tile_ts(uint32_t tmem_d, uint32_t tmem_a, u
         ptx::umma_bf16_ts(tmem_d, tmem_a + k * 8, B_MN ? desc_mnmajor_step(db, k) : desc_kmajor_step(db, ROWS_B, k), idesc,
                           (accumulate || k != 0) ? 1u : 0u);
 }
+
+#ifdef FTL_ATTN_DEBUG
+// Timestamp probe (tools/attn_probe.py builds a separate library with this defined): CTA 0 records clock64 at fixed
+// points of its first item, per key tile.  Slots 0-7 math thread (warp 2 lane 0), 8-15 MMA thread.
+__device__ long long g_attn_dbg[64 * 16];
+#define ATTN_DBG(cond, tile, slot) do { if (blockIdx.x == 0 && (cond) && (tile) < 64) g_attn_dbg[(tile) * 16 + (slot)] = clock64(); } while (0)
+#else
+#define ATTN_DBG(cond, tile, slot) do { } while (0)
+#endif
 
 // ================================================================================================= forward
 // Software pipeline (per CTA): the MMA warp issues S(j+1) as soon as K(j+1) has landed, i.e. while the math threads
@@ -209,19 +220,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 const int st = t & 1, ks = t % NKV;
                 ptx::mbar_wait(&kv_full[ks], (t / NKV) & 1);
                 ptx::tc_fence_after();
+                ATTN_DBG(q_it == 0 && lane == 0, t, 8);
                 if (ptx::elect_one()) {
                     umma_tile<HD / 16, BM, BN, false>(tmem + st * BN, ptx::smem_u32(sQ), ptx::smem_u32(sK + ks * kKBytes), idesc_s, false);
                     ptx::umma_commit(&s_full[st]);
                 }
                 __syncwarp();
+                ATTN_DBG(q_it == 0 && lane == 0, t, 9);
             };
             issue_s(t_it);
             for (int j = 0; j < nkv; ++j, ++t_it) {
                 if (j + 1 < nkv) issue_s(t_it + 1);                   // next scores while the softmax of this tile runs
                 const int st = t_it & 1, ph = (t_it >> 1) & 1, ks = t_it % NKV;
                 ptx::mbar_wait(&p_full[st], ph);                      // P(t) is in smem, S(t) has been read
+                ATTN_DBG(q_it == 0 && lane == 0, t_it, 10);
                 ptx::mbar_wait(&o_empty[st], ph ^ 1);                 // O buffer st (tile t-2) has been folded
                 ptx::tc_fence_after();
+                ATTN_DBG(q_it == 0 && lane == 0, t_it, 11);
                 if (ptx::elect_one()) {
                     // A = P, written by the math threads over the first 64 columns of the score buffer it came from:
                     // only V is fetched from shared memory, which halves the operand traffic of this MMA
@@ -232,6 +247,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                     if (j == nkv - 1) ptx::umma_commit(q_empty);
                 }
                 __syncwarp();
+                ATTN_DBG(q_it == 0 && lane == 0, t_it, 12);
             }
         }
     } else {
@@ -245,6 +261,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
             int b, h, qt; decode(it, b, h, qt);
             const int qi = qt * BM + r;
             float m = -INFINITY, l = 0.f, alpha_prev = 0.f;
+#ifdef FTL_ATTN_DEBUG
+            const bool first = it == (int)blockIdx.x;
+#endif
             float acc[OW];
 #pragma unroll
             for (int d = 0; d < OW; ++d) acc[d] = 0.f;
@@ -252,6 +271,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 const int st = t & 1;
                 ptx::mbar_wait(&o_full[st], (t >> 1) & 1);
                 ptx::tc_fence_after();
+                ATTN_DBG(first && threadIdx.x == 64, t, 6);
                 uint32_t v[OW];
 #pragma unroll
                 for (int c = 0; c < OW; c += 32)
@@ -262,11 +282,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&o_empty[st]);
+                ATTN_DBG(first && threadIdx.x == 64, t, 7);
             };
             for (int j = 0; j <= qt; ++j, ++t_it) {
                 const int st = t_it & 1;
+                ATTN_DBG(first && threadIdx.x == 64, t_it, 0);
                 ptx::mbar_wait(&s_full[st], (t_it >> 1) & 1);
                 ptx::tc_fence_after();
+                ATTN_DBG(first && threadIdx.x == 64, t_it, 1);
                 const uint32_t ts = tmem + st * BN + lane_addr + c0;
                 const bool diag = j == qt;
                 const int lim = diag ? r - c0 : CW;                     // local columns <= lim are visible
@@ -275,6 +298,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
 #pragma unroll
                 for (int c = 0; c < CW; c += 32) ptx::tmem_ld32(ts + c, *reinterpret_cast<uint32_t(*)[32]>(&v[c]));
                 ptx::tmem_ld_wait();
+                ATTN_DBG(first && threadIdx.x == 64, t_it, 2);
                 float mx = -INFINITY;
                 if (!diag) {
 #pragma unroll
@@ -288,6 +312,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 xch[half * BM + r] = mx;
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 mx = fmaxf(mx, xch[(half ^ 1) * BM + r]);
+                ATTN_DBG(first && threadIdx.x == 64, t_it, 3);
                 const float m_new = fmaxf(m, mx * a.scale_log2);
                 const float alpha = exp2f(m - m_new);                   // m = -inf on the first tile -> 0
                 float sum = 0.f;
@@ -303,6 +328,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 }
                 // P overwrites the score buffer in place (both column halves loaded their scores before the exchange
                 // barrier above): columns [c0/2, c0/2 + 32) of this thread's TMEM lane
+                ATTN_DBG(first && threadIdx.x == 64, t_it, 4);
                 ptx::tmem_st32(tmem + st * BN + lane_addr + (c0 >> 1), pk);
                 ptx::tmem_st_wait();
                 l = fmaf(l, alpha, sum);                                // partial over this thread's columns
@@ -310,6 +336,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&p_full[st]);
+                ATTN_DBG(first && threadIdx.x == 64, t_it, 5);
                 if (j > 0) fold(t_it - 1, alpha_prev);                  // runs while the tensor core does P V of this tile
                 alpha_prev = alpha;
             }
@@ -335,6 +362,343 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc<512>(tmem);
+}
+
+// ================================================================================================= forward, two query tiles per CTA
+// The timeline of attn_fwd_kernel (tools/attn_probe.py, profiles/attn_tc_notes.md) shows its math threads busy for
+// ~2850 cycles per 128x128 tile while the tensor pipe needs ~1024: exponentials (MUFU, 16/clk/SM -> 1024 cycles per
+// tile), the row-max exchange barrier between the two column halves and the per-tile fold of O into registers all sit
+// on one serial chain.  This kernel removes the chain instead of shortening it:
+//   * a CTA owns TWO consecutive query tiles A, B of one head (256 rows) which share every K/V tile; softmax warpgroup
+//     A (warps 0-3) and B (warps 4-7) each own whole rows of their tile (no exchange) and run half a step out of
+//     phase, so one group's MUFU phase overlaps the other's TMEM traffic and the tensor pipe alternates
+//     P_A V, Q_A K^T(next), P_B V, Q_B K^T(next);
+//   * O accumulates in TMEM across key tiles (accumulate flag); rescaling is LAZY: a row changes its reference maximum
+//     only when the running maximum grew by more than 2^8, so the correction warpgroup (warps 8-11) almost never has
+//     to touch O and the softmax warps never do.  P <= 2^8 is harmless in bf16 (same relative precision) and the row
+//     sum uses the same reference, so lse = m_ref + log2(l) is exact;
+//   * the correction warpgroup also does the epilogue (O / l -> bf16 -> global), off the softmax warps' path;
+//   * work items are handed out by an atomic counter, heaviest (latest query tiles) first: causal items differ 10x in
+//     length and a static round-robin leaves a third of the SMs idle at the end.
+// TMEM columns: S_A [0,128) S_B [128,256) (P overwrites the first 64 columns of its S), O_A at 256, O_B at 256 + HD.
+// The scheduler words are file-scope and reset by the last CTA to drain the queue, so launches of this kernel must be
+// ordered on ONE stream per device (they are: attention runs on the compute stream only).
+constexpr int kFwd2Threads = 512;   // warps 0-3 softmax A, 4-7 softmax B, 8-11 correction + epilogue, 12 TMA, 13 MMA, 14-15 idle
+// Register budgets after setmaxnreg (per thread; 64K per SM = 512 x 128 at launch): the softmax warpgroups hold a whole
+// score row, the others give registers up.  2 x 128 x 176 + 128 x 80 + 128 x 80 = 65536.
+constexpr int kRegSoftmax = 176, kRegCorr = 80, kRegIssue = 80;
+constexpr float kRescaleThreshold = 8.f;
+__device__ int g_fwd2_sched[2];     // [0] next work item, [1] CTAs that have seen the end of the queue
+
+template <int HD>
+__global__ void __launch_bounds__(kFwd2Threads, 1)
+attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
+    constexpr int BM = 128, BN = 128;
+    constexpr int kTile = BN * HD * 2;                // bytes of one Q, K or V tile
+    constexpr int NST = 5;                            // K/V ring: K(0) V(0) K(1) V(1) ...
+    constexpr int kTmemO = 2 * BN;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;                               // Q_A, Q_B
+    uint8_t* sKV = sQ + 2 * kTile;                    // NST tiles
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + NST * kTile);
+    uint64_t* q_full = bars;            // 1
+    uint64_t* q_empty = bars + 1;       // 1
+    uint64_t* kv_full = bars + 2;       // NST (<= 6)
+    uint64_t* kv_empty = bars + 8;      // NST
+    uint64_t* s_full = bars + 14;       // [2]  per query tile X
+    uint64_t* p_full = bars + 16;       // [2]
+    uint64_t* o_ready = bars + 18;      // [2]  O_X may be accumulated into (rescaled / drained)
+    uint64_t* o_full = bars + 20;       // [2]  P_X V of a step has completed
+    uint64_t* alpha_full = bars + 22;   // [2]
+    uint64_t* l_full = bars + 24;       // [2]
+    float* sAlpha = reinterpret_cast<float*>(bars + 26);   // [2][BM]
+    float* sL = sAlpha + 2 * BM;                            // [2][BM]
+    int* sItem = reinterpret_cast<int*>(sL + 2 * BM);       // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sItem + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q_pairs = a.S / (2 * BM);
+    const int items = a.B * a.H * q_pairs;
+    const int rep = a.H / a.KV;
+
+    if (warp == 13 && lane == 0) {
+        ptx::prefetch_tmap(&tmQKV);
+        ptx::mbar_init(q_full, 1); ptx::mbar_init(q_empty, 1);
+        for (int i = 0; i < NST; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_full[i], 4); ptx::mbar_init(&o_ready[i], 4);
+            ptx::mbar_init(&o_full[i], 1); ptx::mbar_init(&alpha_full[i], 4); ptx::mbar_init(&l_full[i], 4);
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 12) ptx::tmem_alloc<512>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    // item -> (b, h, pair): latest pairs (longest loops) first; neighbouring items are the heads of one kv group
+    auto decode = [&](int it, int& b, int& h, int& p) {
+        p = q_pairs - 1 - it / (a.B * a.H);
+        const int r = it % (a.B * a.H);
+        b = r / a.H; h = r % a.H;
+    };
+
+    if (warp >= 12) {
+        ptx::reg_dec<kRegIssue>();
+        if (warp == 12) {
+        // ------------------------------------------------------------------------------------------ TMA producer
+        if (ptx::elect_one()) {
+            int kv_n = 0;
+            for (int q_it = 0;; ++q_it) {
+                const int it = atomicAdd(&g_fwd2_sched[0], 1);
+                ptx::mbar_wait(q_empty, (q_it & 1) ^ 1);           // Q tiles and the item slot of two items ago are free
+                if (it >= items) { sItem[q_it & 1] = -1; ptx::mbar_arrive(q_full); break; }
+                sItem[q_it & 1] = it;
+                int b, h, p; decode(it, b, h, p);
+                const int g = h / rep;
+                const int row0 = b * a.S + p * 2 * BM;
+                ptx::mbar_arrive_expect_tx(q_full, 2 * kTile);
+#pragma unroll
+                for (int x = 0; x < 2; ++x)
+#pragma unroll
+                    for (int c = 0; c < HD / 64; ++c)
+                        ptx::tma_load_2d(sQ + x * kTile + c * BM * 128, &tmQKV, q_full, h * HD + c * 64, row0 + x * BM);
+                const int nB = 2 * p + 2;
+                for (int j = 0; j < nB; ++j) {
+                    const int krow = b * a.S + j * BN;
+#pragma unroll
+                    for (int kv = 0; kv < 2; ++kv, ++kv_n) {       // K(j) then V(j)
+                        const int st = kv_n % NST;
+                        ptx::mbar_wait(&kv_empty[st], ((kv_n / NST) & 1) ^ 1);
+                        ptx::mbar_arrive_expect_tx(&kv_full[st], kTile);
+                        const int col = (a.H + kv * a.KV + g) * HD;
+#pragma unroll
+                        for (int c = 0; c < HD / 64; ++c)
+                            ptx::tma_load_2d(sKV + st * kTile + c * BN * 128, &tmQKV, &kv_full[st], col + c * 64, krow);
+                    }
+                }
+            }
+            __threadfence();
+            if (atomicAdd(&g_fwd2_sched[1], 1) == (int)gridDim.x - 1) {   // every CTA has fetched its last item
+                g_fwd2_sched[0] = 0; g_fwd2_sched[1] = 0;
+                __threadfence();
+            }
+        }
+        } else if (warp == 13) {
+        // ------------------------------------------------------------------------------------------ MMA issuer
+        constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(BM, BN, false, false);
+        constexpr uint32_t idesc_o = ptx::umma_idesc_bf16(BM, HD, false, true);   // B = V is MN-major
+        int cx[2] = {0, 0};                                                        // tiles done per query tile (phases)
+        int kv0 = 0;                                                               // ring index of K(0) of this item
+        for (int q_it = 0;; ++q_it) {
+            ptx::mbar_wait(q_full, q_it & 1);
+            const int it = sItem[q_it & 1];
+            if (it < 0) break;
+            int b, h, p; decode(it, b, h, p);
+            const int nB = 2 * p + 2;
+            auto issue_s = [&](int x, int j) {                                     // S_X = Q_X K(j)^T
+                const int kn = kv0 + 2 * j, ks = kn % NST;
+                ptx::mbar_wait(&kv_full[ks], (kn / NST) & 1);
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) {
+                    umma_tile<HD / 16, BM, BN, false>(tmem + x * BN, ptx::smem_u32(sQ + x * kTile), ptx::smem_u32(sKV + ks * kTile),
+                                                      idesc_s, false);
+                    ptx::umma_commit(&s_full[x]);
+                    if (x == 1) {
+                        ptx::umma_commit(&kv_empty[ks]);                           // B is the last reader of every K tile
+                        if (j == nB - 1) ptx::umma_commit(q_empty);                // ... and of the Q tiles
+                    }
+                }
+                __syncwarp();
+            };
+            issue_s(0, 0);
+            issue_s(1, 0);
+            for (int j = 0; j < nB; ++j) {
+#pragma unroll
+                for (int x = 0; x < 2; ++x) {
+                    const int nx = nB - 1 + x;                                     // A: 2p + 1 key tiles, B: 2p + 2
+                    if (j >= nx) continue;
+                    const int ph = cx[x] & 1;
+                    const int vn = kv0 + 2 * j + 1, vs = vn % NST;
+                    ptx::mbar_wait(&kv_full[vs], (vn / NST) & 1);
+                    ptx::mbar_wait(&o_ready[x], ph);                               // O_X rescaled (or drained, j = 0)
+                    ptx::mbar_wait(&p_full[x], ph);                                // P_X(j) is in TMEM
+                    ptx::tc_fence_after();
+                    ATTN_DBG(q_it == 0 && lane == 0 && x == 0, j, 10);
+                    if (ptx::elect_one()) {
+                        umma_tile_ts<BN / 16, BN, true>(tmem + kTmemO + x * HD, tmem + x * BN, ptx::smem_u32(sKV + vs * kTile),
+                                                        idesc_o, j > 0);
+                        ptx::umma_commit(&o_full[x]);
+                        if (x == 1) ptx::umma_commit(&kv_empty[vs]);
+                    }
+                    __syncwarp();
+                    ++cx[x];
+                    if (j + 1 < nx) issue_s(x, j + 1);                             // executes after P_X V: S_X may be overwritten
+                    ATTN_DBG(q_it == 0 && lane == 0 && x == 0, j, 11);
+                }
+            }
+            kv0 += 2 * nB;
+        }
+        }
+    } else if (warp < 8) {
+        // ------------------------------------------------------------------------------------------ softmax A / B
+        ptx::reg_inc<kRegSoftmax>();
+        const int x = warp >> 2, q = warp & 3;
+        const int r = q * 32 + lane;                                   // query row inside the tile = TMEM lane
+        const uint32_t ts = tmem + x * BN + ((uint32_t)(q * 32) << 16);
+        int c = 0;
+        for (int q_it = 0;; ++q_it) {
+            ptx::mbar_wait(q_full, q_it & 1);
+            const int it = sItem[q_it & 1];
+            if (it < 0) break;
+            int b, h, p; decode(it, b, h, p);
+            const int qt = 2 * p + x;
+            float m = -INFINITY, l = 0.f;
+            for (int j = 0; j <= qt; ++j, ++c) {
+                ATTN_DBG(q_it == 0 && threadIdx.x == 0, j, 0);
+                ptx::mbar_wait(&s_full[x], c & 1);
+                ptx::tc_fence_after();
+                ATTN_DBG(q_it == 0 && threadIdx.x == 0, j, 1);
+                ATTN_DBG(q_it == 0 && threadIdx.x == 128, j, 5);
+                // The whole score row lives in registers (this warpgroup raised its register budget for it): one TMEM
+                // round trip (~150 cycles) per tile instead of one per chunk and pass.  The diagonal tile (columns <= r
+                // visible) is a separate instantiation so that the other tiles carry no compare / select per element.
+                float alpha = 1.f, sum = 0.f;
+                auto tile = [&](auto diag_c) {
+                    constexpr bool DIAG = decltype(diag_c)::value;
+                    uint32_t v[BN];
+#pragma unroll
+                    for (int cb = 0; cb < BN; cb += 32) ptx::tmem_ld32(ts + cb, *reinterpret_cast<uint32_t(*)[32]>(&v[cb]));
+                    ptx::tmem_ld_wait();
+                    // row maximum, four independent chains (one dependent chain of 128 costs ~500 cycles)
+                    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+                    for (int i = 0; i < BN; ++i)
+                        if (!DIAG || i <= r) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(v[i]));
+                    const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+                    const float m_new = fmaxf(m, mx * a.scale_log2);
+                    if (j == 0) m = m_new;                               // O is overwritten by the first P V: no rescale
+                    else if (m_new - m > kRescaleThreshold) { alpha = ptx::ex2(m - m_new); m = m_new; }
+                    if (j > 0) {
+                        sAlpha[x * BM + r] = alpha;
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(&alpha_full[x]);
+                    }
+                    ATTN_DBG(q_it == 0 && threadIdx.x == 0, j, 2);
+                    ATTN_DBG(q_it == 0 && threadIdx.x == 128, j, 6);
+                    // P = exp2(s * scale - m): packed f32x2 multiply-add and add (two elements per issue slot), MUFU.EX2,
+                    // bf16 pairs written over the scores (all of them are in registers by now)
+                    const uint64_t sc2 = ptx::pack_f32x2(a.scale_log2, a.scale_log2), nm2 = ptx::pack_f32x2(-m, -m);
+                    uint64_t sum2[4] = {0ull, 0ull, 0ull, 0ull};
+#pragma unroll
+                    for (int cb = 0; cb < BN; cb += 32) {
+                        uint32_t pk[16];
+#pragma unroll
+                        for (int i = 0; i < 32; i += 2) {
+                            float x0, x1;
+                            ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(v[cb + i]), __uint_as_float(v[cb + i + 1])), sc2, nm2), x0, x1);
+                            float e0 = ptx::ex2(x0), e1 = ptx::ex2(x1);
+                            if (DIAG) {
+                                if (cb + i > r) e0 = 0.f;
+                                if (cb + i + 1 > r) e1 = 0.f;
+                            }
+                            sum2[(i >> 1) & 3] = ptx::add_f32x2(sum2[(i >> 1) & 3], ptx::pack_f32x2(e0, e1));
+                            pk[i >> 1] = ptx::pack_bf16x2(e0, e1);
+                        }
+                        ptx::tmem_st16(ts + (cb >> 1), pk);
+                    }
+                    float s0, s1;
+                    ptx::unpack_f32x2(ptx::add_f32x2(ptx::add_f32x2(sum2[0], sum2[1]), ptx::add_f32x2(sum2[2], sum2[3])), s0, s1);
+                    sum = s0 + s1;
+                };
+                if (j == qt) tile(std::true_type{}); else tile(std::false_type{});
+                ptx::tmem_st_wait();
+                ATTN_DBG(q_it == 0 && threadIdx.x == 0, j, 3);
+                ATTN_DBG(q_it == 0 && threadIdx.x == 128, j, 7);
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&p_full[x]);
+                l = fmaf(l, alpha, sum);
+                ATTN_DBG(q_it == 0 && threadIdx.x == 0, j, 4);
+                ATTN_DBG(q_it == 0 && threadIdx.x == 128, j, 8);
+            }
+            sL[x * BM + r] = l;
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&l_full[x]);
+            a.lse[((int64_t)b * a.H + h) * a.S + qt * BM + r] = m + log2f(l);
+        }
+    } else {
+        // ------------------------------------------------------------------------------------------ correction + epilogue
+        ptx::reg_dec<kRegCorr>();
+        const int q = warp & 3;
+        const int r = q * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        int cx[2] = {0, 0}, ax[2] = {0, 0};
+        for (int q_it = 0;; ++q_it) {
+            ptx::mbar_wait(q_full, q_it & 1);
+            const int it = sItem[q_it & 1];
+            if (it < 0) break;
+            int b, h, p; decode(it, b, h, p);
+            const int nB = 2 * p + 2;
+            for (int j = 0; j < nB; ++j) {
+#pragma unroll
+                for (int x = 0; x < 2; ++x) {
+                    if (j >= nB - 1 + x) continue;
+                    if (j > 0) {
+                        ptx::mbar_wait(&alpha_full[x], ax[x] & 1);
+                        ++ax[x];
+                        const float alpha = sAlpha[x * BM + r];
+                        if (__any_sync(0xffffffffu, alpha != 1.f)) {
+                            ptx::mbar_wait(&o_full[x], (cx[x] - 1) & 1);            // P_X V (j-1) has completed
+                            ptx::tc_fence_after();
+                            const uint32_t to = tmem + kTmemO + x * HD + lane_addr;
+#pragma unroll
+                            for (int d = 0; d < HD; d += 32) {
+                                uint32_t v[32];
+                                ptx::tmem_ld32(to + d, v);
+                                ptx::tmem_ld_wait();
+#pragma unroll
+                                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+                                ptx::tmem_st32(to + d, v);
+                            }
+                            ptx::tmem_st_wait();
+                        }
+                    }
+                    ptx::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive(&o_ready[x]);
+                    ++cx[x];
+                }
+            }
+#pragma unroll
+            for (int x = 0; x < 2; ++x) {
+                ptx::mbar_wait(&o_full[x], (cx[x] - 1) & 1);
+                ptx::mbar_wait(&l_full[x], q_it & 1);
+                ptx::tc_fence_after();
+                const float inv = 1.f / sL[x * BM + r];
+                const uint32_t to = tmem + kTmemO + x * HD + lane_addr;
+                __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + (2 * p + x) * BM + r) * a.ld_out + h * HD;
+#pragma unroll
+                for (int d = 0; d < HD; d += 32) {
+                    uint32_t v[32];
+                    ptx::tmem_ld32(to + d, v);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; i += 8) {
+                        float o[8];
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) o[k] = __uint_as_float(v[i + k]) * inv;
+                        st8(orow + d + i, pack8(o));
+                    }
+                }
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 12) ptx::tmem_dealloc<512>(tmem);
 }
 
 // ================================================================================================= delta
@@ -869,6 +1233,12 @@ using namespace ftl;
 
 // qkv: [B*S, ld_qkv] fused projection (q heads | k heads | v heads), RoPE already applied to q and k.
 // out: [B*S, H*hd]; lse: fp32 [B, H, S].  S must be a multiple of 128; hd in {64, 128}.
+#ifdef FTL_ATTN_DEBUG
+FTL_API int ftl_attn_dbg_read(long long* host) {
+    return (int)cudaMemcpyFromSymbol(host, g_attn_dbg, sizeof(g_attn_dbg));
+}
+#endif
+
 FTL_API int ftl_attn_fwd(const void* qkv, int64_t ld_qkv, void* out, int64_t ld_out, float* lse, int B, int S, int H, int KV,
                          int hd, cudaStream_t stream) {
     if (S % 128 || (hd != 64 && hd != 128) || H % KV || ld_qkv % 8 || ld_out % 8) return (int)cudaErrorInvalidValue;
@@ -879,6 +1249,21 @@ FTL_API int ftl_attn_fwd(const void* qkv, int64_t ld_qkv, void* out, int64_t ld_
     a.out = (__nv_bfloat16*)out; a.ld_out = ld_out; a.lse = lse;
     a.B = B; a.S = S; a.H = H; a.KV = KV; a.ld_qkv = (int)ld_qkv;
     a.scale = 1.f / sqrtf((float)hd); a.scale_log2 = a.scale * kLog2e;
+    static const bool use_v1 = [] { const char* v = getenv("FTL_ATTN_FWD"); return v && v[0] == '1'; }();
+    if (S % 256 == 0 && !use_v1) {      // two query tiles per CTA, dynamic scheduler (see attn_fwd2_kernel)
+        const int items2 = B * H * (S / 256);
+        const int grid2 = items2 < kNumSMs ? items2 : kNumSMs;
+        if (hd == 128) {
+            constexpr int smem = 128 * 128 * 2 * 7 + 26 * 8 + 2048 + 16;
+            static bool once = false; if (!once) { if ((e = set_smem(attn_fwd2_kernel<128>, smem))) return e; once = true; }
+            attn_fwd2_kernel<128><<<grid2, kFwd2Threads, smem, stream>>>(tm, a);
+        } else {
+            constexpr int smem = 128 * 64 * 2 * 7 + 26 * 8 + 2048 + 16;
+            static bool once = false; if (!once) { if ((e = set_smem(attn_fwd2_kernel<64>, smem))) return e; once = true; }
+            attn_fwd2_kernel<64><<<grid2, kFwd2Threads, smem, stream>>>(tm, a);
+        }
+        return (int)cudaGetLastError();
+    }
     const int items = B * H * (S / 128);
     const int grid = items < kNumSMs ? items : kNumSMs;
     if (hd == 128) {
