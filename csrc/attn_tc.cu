@@ -388,6 +388,7 @@ constexpr int kFwd2Threads = 512;   // warps 0-3 softmax A, 4-7 softmax B, 8-11 
 // score row, the others give registers up.  2 x 128 x 176 + 128 x 80 + 128 x 80 = 65536.
 constexpr int kRegSoftmax = 176, kRegCorr = 80, kRegIssue = 80;
 constexpr float kRescaleThreshold = 8.f;
+constexpr int kPolyEvery = 2;       // one pair of exponentials in kPolyEvery goes to the FMA pipe
 __device__ int g_fwd2_sched[2];     // [0] next work item, [1] CTAs that have seen the end of the queue
 
 template <int HD>
@@ -453,7 +454,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
             int kv_n = 0;
             for (int q_it = 0;; ++q_it) {
                 const int it = atomicAdd(&g_fwd2_sched[0], 1);
-                ptx::mbar_wait(q_empty, (q_it & 1) ^ 1);           // Q tiles and the item slot of two items ago are free
+                ptx::mbar_wait_sleep(q_empty, (q_it & 1) ^ 1);           // Q tiles and the item slot of two items ago are free
                 if (it >= items) { sItem[q_it & 1] = -1; ptx::mbar_arrive(q_full); break; }
                 sItem[q_it & 1] = it;
                 int b, h, p; decode(it, b, h, p);
@@ -471,7 +472,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
 #pragma unroll
                     for (int kv = 0; kv < 2; ++kv, ++kv_n) {       // K(j) then V(j)
                         const int st = kv_n % NST;
-                        ptx::mbar_wait(&kv_empty[st], ((kv_n / NST) & 1) ^ 1);
+                        ptx::mbar_wait_sleep(&kv_empty[st], ((kv_n / NST) & 1) ^ 1);
                         ptx::mbar_arrive_expect_tx(&kv_full[st], kTile);
                         const int col = (a.H + kv * a.KV + g) * HD;
 #pragma unroll
@@ -592,14 +593,24 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                     // bf16 pairs written over the scores (all of them are in registers by now)
                     const uint64_t sc2 = ptx::pack_f32x2(a.scale_log2, a.scale_log2), nm2 = ptx::pack_f32x2(-m, -m);
                     uint64_t sum2[4] = {0ull, 0ull, 0ull, 0ull};
+                    // Every second pair of exponentials is evaluated on the FMA pipe (ptx::exp2_poly_x2) instead of the
+                    // special-function unit: MUFU.EX2 delivers 16 results / clk / SM, which for a 128 x 128 tile is as
+                    // long as its two MMAs (1024 cycles), and the polynomial pairs fill the issue slots in which a
+                    // MUFU result is still in flight.
 #pragma unroll
                     for (int cb = 0; cb < BN; cb += 32) {
                         uint32_t pk[16];
 #pragma unroll
                         for (int i = 0; i < 32; i += 2) {
-                            float x0, x1;
-                            ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(v[cb + i]), __uint_as_float(v[cb + i + 1])), sc2, nm2), x0, x1);
-                            float e0 = ptx::ex2(x0), e1 = ptx::ex2(x1);
+                            const uint64_t x2 = ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(v[cb + i]), __uint_as_float(v[cb + i + 1])), sc2, nm2);
+                            float e0, e1;
+                            if ((i >> 1) % kPolyEvery == kPolyEvery - 1) {
+                                ptx::exp2_poly_x2(x2, e0, e1);
+                            } else {
+                                float x0, x1;
+                                ptx::unpack_f32x2(x2, x0, x1);
+                                e0 = ptx::ex2(x0); e1 = ptx::ex2(x1);
+                            }
                             if (DIAG) {
                                 if (cb + i > r) e0 = 0.f;
                                 if (cb + i + 1 > r) e1 = 0.f;
@@ -637,7 +648,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
         const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
         int cx[2] = {0, 0}, ax[2] = {0, 0};
         for (int q_it = 0;; ++q_it) {
-            ptx::mbar_wait(q_full, q_it & 1);
+            ptx::mbar_wait_sleep(q_full, q_it & 1);
             const int it = sItem[q_it & 1];
             if (it < 0) break;
             int b, h, p; decode(it, b, h, p);
@@ -647,11 +658,11 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                 for (int x = 0; x < 2; ++x) {
                     if (j >= nB - 1 + x) continue;
                     if (j > 0) {
-                        ptx::mbar_wait(&alpha_full[x], ax[x] & 1);
+                        ptx::mbar_wait_sleep(&alpha_full[x], ax[x] & 1);
                         ++ax[x];
                         const float alpha = sAlpha[x * BM + r];
                         if (__any_sync(0xffffffffu, alpha != 1.f)) {
-                            ptx::mbar_wait(&o_full[x], (cx[x] - 1) & 1);            // P_X V (j-1) has completed
+                            ptx::mbar_wait_sleep(&o_full[x], (cx[x] - 1) & 1);            // P_X V (j-1) has completed
                             ptx::tc_fence_after();
                             const uint32_t to = tmem + kTmemO + x * HD + lane_addr;
 #pragma unroll
@@ -674,8 +685,8 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
             }
 #pragma unroll
             for (int x = 0; x < 2; ++x) {
-                ptx::mbar_wait(&o_full[x], (cx[x] - 1) & 1);
-                ptx::mbar_wait(&l_full[x], q_it & 1);
+                ptx::mbar_wait_sleep(&o_full[x], (cx[x] - 1) & 1);
+                ptx::mbar_wait_sleep(&l_full[x], q_it & 1);
                 ptx::tc_fence_after();
                 const float inv = 1.f / sL[x * BM + r];
                 const uint32_t to = tmem + kTmemO + x * HD + lane_addr;

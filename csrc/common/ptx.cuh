@@ -60,7 +60,30 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const uint64_t t0 = global_timer_ns();
+#ifdef FTL_ATTN_DEBUG
+    bool said = false;
     while (!mbar_try_wait(bar, parity)) {
+        const uint64_t dt = global_timer_ns() - t0;
+        if (dt > 2000000000ull && !said) {
+            said = true;
+            if (blockIdx.x == 0) printf("mbarrier stuck: thread %d barrier@%u parity %u\n", threadIdx.x, smem_u32(bar), parity);
+        }
+        if (dt > 4000000000ull) __trap();
+    }
+#else
+    while (!mbar_try_wait(bar, parity)) {
+        if (global_timer_ns() - t0 > 4000000000ull) __trap();
+    }
+#endif
+}
+
+// Same budget, but the thread sleeps between polls: for warps whose wake-up latency is not on the critical path and
+// whose polling would otherwise compete for issue slots with the warps doing the math on the same scheduler.
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns = 200) {
+    if (mbar_try_wait(bar, parity)) return;
+    const uint64_t t0 = global_timer_ns();
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(ns);
         if (global_timer_ns() - t0 > 4000000000ull) __trap();
     }
 }
@@ -216,6 +239,26 @@ __device__ __forceinline__ float ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+}
+// 2^x for a packed pair WITHOUT the special-function unit: x = n + f with n = round(x), f in [-0.5, 0.5];
+// 2^f by a degree-3 polynomial (relative error 1.6e-4, far below bf16's 2^-9) and 2^n by adding n to the exponent bits.
+// n comes from the magic-number trick: after t = x + 1.5 * 2^23 the low mantissa bits of t hold n in two's complement.
+// ~5 issue slots per element on the FMA / ALU pipes against 8 cycles of MUFU occupancy.  Inputs are clamped at -125.
+__device__ __forceinline__ void exp2_poly_x2(uint64_t x2, float& e0, float& e1) {
+    float x0, x1;
+    unpack_f32x2(x2, x0, x1);
+    const uint64_t xc = pack_f32x2(fmaxf(x0, -125.f), fmaxf(x1, -125.f));
+    const uint64_t t = add_f32x2(xc, pack_f32x2(12582912.f, 12582912.f));
+    const uint64_t n = add_f32x2(t, pack_f32x2(-12582912.f, -12582912.f));
+    const uint64_t f = fma_f32x2(n, pack_f32x2(-1.f, -1.f), xc);
+    uint64_t p = fma_f32x2(f, pack_f32x2(0.05360212177038193f, 0.05360212177038193f), pack_f32x2(0.24237291514873505f, 0.24237291514873505f));
+    p = fma_f32x2(p, f, pack_f32x2(0.6935023665428162f, 0.6935023665428162f));
+    p = fma_f32x2(p, f, pack_f32x2(0.9999481439590454f, 0.9999481439590454f));
+    float p0, p1, t0, t1;
+    unpack_f32x2(p, p0, p1);
+    unpack_f32x2(t, t0, t1);
+    e0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+    e1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
 }
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     uint32_t r;
