@@ -124,8 +124,10 @@ __device__ __forceinline__ void umma_tile_ts(uint32_t tmem_d, uint32_t tmem_a, u
 // points of its first item, per key tile.  Slots 0-7 math thread (warp 2 lane 0), 8-15 MMA thread.
 __device__ long long g_attn_dbg[64 * 16];
 #define ATTN_DBG(cond, tile, slot) do { if (blockIdx.x == 0 && (cond) && (tile) < 64) g_attn_dbg[(tile) * 16 + (slot)] = clock64(); } while (0)
+#define KV_DBG(cond, tile, slot) do { if (blockIdx.x == 0 && (cond) && (tile) < 64) g_attn_dbg[(tile) * 16 + (slot)] = clock64(); } while (0)
 #else
 #define ATTN_DBG(cond, tile, slot) do { } while (0)
+#define KV_DBG(cond, tile, slot) do { } while (0)
 #endif
 
 // ================================================================================================= forward
@@ -843,6 +845,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             const int st = t & 1, qs = t % NQ;
             ptx::mbar_wait(&q_full[qs], (t / NQ) & 1);
             ptx::tc_fence_after();
+            KV_DBG(item_it == 0 && lane == 0, t, 8);
             if (ptx::elect_one()) {
                 const uint32_t qb = ptx::smem_u32(sQ + qs * kQBytes), dob = ptx::smem_u32(sDO + qs * kQBytes);
                 umma_tile<HD / 16, BK, BQ, false>(tmem + st * 128, ka, qb, idesc_st, false);
@@ -861,19 +864,29 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             for (int n = 0; n < inner; ++n, ++n_it) {
                 if (n + 1 < inner) issue_sdp(n_it + 1);               // next scores run under the math of this iteration
                 const int st = n_it & 1;
+                KV_DBG(item_it == 0 && lane == 0, n, 9);
                 ptx::mbar_wait(&t_full[st], (n_it >> 1) & 1);
                 ptx::tc_fence_after();
+                KV_DBG(item_it == 0 && lane == 0, n, 10);
                 if (ptx::elect_one()) {
                     const int qs = n_it % NQ;
                     const uint32_t qb = ptx::smem_u32(sQ + qs * kQBytes), dob = ptx::smem_u32(sDO + qs * kQBytes);
-                    const uint32_t pt = ptx::smem_u32(sPT + st * kTBytes), dst = ptx::smem_u32(sDST + st * kTBytes);
-                    umma_tile<BQ / 16, BK, BQ, true>(tmem + kTmDV, pt, dob, idesc_acc, n != 0);
-                    umma_tile<BQ / 16, BK, BQ, true>(tmem + kTmDK, dst, qb, idesc_acc, n != 0);
+                    // A = P^T / dS^T from TMEM: queries 0-31 sit in columns [0,16) of the score buffer, 32-63 in [32,48)
+                    const uint64_t d_do = desc_mnmajor0(dob, BQ), d_q = desc_mnmajor0(qb, BQ);
+#pragma unroll
+                    for (int k = 0; k < BQ / 16; ++k)
+                        ptx::umma_bf16_ts(tmem + kTmDV, tmem + st * 128 + (k >> 1) * 32 + (k & 1) * 8, desc_mnmajor_step(d_do, k), idesc_acc,
+                                          (n != 0 || k != 0) ? 1u : 0u);
+#pragma unroll
+                    for (int k = 0; k < BQ / 16; ++k)
+                        ptx::umma_bf16_ts(tmem + kTmDK, tmem + st * 128 + kTmDP + (k >> 1) * 32 + (k & 1) * 8, desc_mnmajor_step(d_q, k), idesc_acc,
+                                          (n != 0 || k != 0) ? 1u : 0u);
                     ptx::umma_commit(&t_empty[st]);
                     ptx::umma_commit(&q_empty[qs]);
                     if (n == inner - 1) { ptx::umma_commit(acc_full); ptx::umma_commit(kv_empty); }
                 }
                 __syncwarp();
+                KV_DBG(item_it == 0 && lane == 0, n, 11);
             }
         }
     } else {
@@ -882,6 +895,11 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
         const int tid = threadIdx.x - 64;                              // 0..255
         const int half = (warp - 2) >> 2;                              // which 32 of the 64 query columns / which half of hd
+        const int c0 = half * 32;
+        uint32_t st_off[4];                                            // swizzled offsets of this thread's four 16-byte stores
+#pragma unroll
+        for (int u = 0; u < 4; ++u) st_off[u] = r * 128 + (((half * 4 + u) ^ (r & 7)) << 4);
+        const uint64_t scale2 = ptx::pack_f32x2(a.scale_log2, a.scale_log2);
         int item_it = 0, n_it = 0;
         for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
             int b, g, kt, n0, n1; bool whole;
@@ -901,48 +919,76 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     const int qt = 2 * kt + qo;
                     float* lse_s = sLse + (n_it & 1) * BQ;
                     float* del_s = sDelta + (n_it & 1) * BQ;
-                    if (tid < BQ) { lse_s[tid] = lse_r; del_s[tid] = del_r; }
+                    if (tid < BQ) { lse_s[tid] = -lse_r; del_s[tid] = -del_r; }   // negated: operands of packed adds
                     if (++qo == nq) { qo = 0; ++hh; }
                     if (tid < BQ && n + 1 < n1) {
                         const int64_t o = ((int64_t)b * a.H + g * rep + hh) * a.S + (2 * kt + qo) * BQ + tid;
                         lse_r = a.lse[o]; del_r = a.delta[o];
                     }
+                    KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 0);
                     asm volatile("bar.sync 1, 256;" ::: "memory");
+                    KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 1);
                     const int st = n_it & 1;
                     ptx::mbar_wait(&s_full[st], (n_it >> 1) & 1);
+                    KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 2);
                     ptx::mbar_wait(&t_empty[st], ((n_it >> 1) & 1) ^ 1);   // dV/dK of iteration n-2 no longer read this buffer
                     ptx::tc_fence_after();
+                    KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 3);
                     const bool diag = qt * BQ < kt * BK + BK;          // tile touches the diagonal: mask q < key
-                    const uint32_t ptb = ptx::smem_u32(sPT + st * kTBytes), dstb = ptx::smem_u32(sDST + st * kTBytes);
-                    {
-                        const int c = half * 32;
-                        uint32_t sv[32], dv[32];
-                        ptx::tmem_ld32(tmem + st * 128 + lane_addr + c, sv);
-                        ptx::tmem_ld32(tmem + st * 128 + kTmDP + lane_addr + c, dv);
+                    // P^T = exp2(S^T * scale - lse[q]), dS^T = P^T * (dP^T - delta[q]) on packed fp32 pairs: per two elements
+                    // one FFMA2, two MUFU, one FADD2, one FMUL2, two F2FP (the scalar version spent ~18 issue slots per
+                    // element and made instruction issue, not the tensor pipe, the limiter of this kernel).  -lse and
+                    // -delta arrive from shared memory already paired; the diagonal block is a separate instantiation.
+                    auto block = [&](auto diag_c) {
+                        constexpr bool DIAG = decltype(diag_c)::value;
+                        uint32_t sv[32], dv[32], pt[16], dst[16];
+                        ptx::tmem_ld32(tmem + st * 128 + lane_addr + c0, sv);
+                        ptx::tmem_ld32(tmem + st * 128 + kTmDP + lane_addr + c0, dv);
                         ptx::tmem_ld_wait();
+                        KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 4);
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
-                            float p[8], ds[8], ls[8], dl[8];
-                            *reinterpret_cast<float4*>(ls) = *reinterpret_cast<const float4*>(lse_s + c + u * 8);
-                            *reinterpret_cast<float4*>(ls + 4) = *reinterpret_cast<const float4*>(lse_s + c + u * 8 + 4);
-                            *reinterpret_cast<float4*>(dl) = *reinterpret_cast<const float4*>(del_s + c + u * 8);
-                            *reinterpret_cast<float4*>(dl + 4) = *reinterpret_cast<const float4*>(del_s + c + u * 8 + 4);
+                            const ulonglong2 la = *reinterpret_cast<const ulonglong2*>(lse_s + c0 + u * 8);
+                            const ulonglong2 lb = *reinterpret_cast<const ulonglong2*>(lse_s + c0 + u * 8 + 4);
+                            const ulonglong2 da = *reinterpret_cast<const ulonglong2*>(del_s + c0 + u * 8);
+                            const ulonglong2 db = *reinterpret_cast<const ulonglong2*>(del_s + c0 + u * 8 + 4);
+#ifdef FTL_ATTN_NOLDS
+                            const uint64_t nl[4] = {scale2, scale2, scale2, scale2}, nd[4] = {scale2, scale2, scale2, scale2};
+#else
+                            const uint64_t nl[4] = {la.x, la.y, lb.x, lb.y}, nd[4] = {da.x, da.y, db.x, db.y};
+#endif
+                            uint32_t pp[4], dd[4];
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                const int col = c + u * 8 + i;
-                                float e = exp2f(fmaf(__uint_as_float(sv[u * 8 + i]), a.scale_log2, -ls[i]));
-                                if (diag && qt * BQ + col < kj) e = 0.f;
-                                p[i] = e;
-                                ds[i] = e * (__uint_as_float(dv[u * 8 + i]) - dl[i]);
+                            for (int k = 0; k < 4; ++k) {
+                                const int i = u * 8 + 2 * k;
+                                float x0, x1;
+                                ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), scale2, nl[k]), x0, x1);
+                                float e0 = ptx::ex2(x0), e1 = ptx::ex2(x1);
+                                if (DIAG) {
+                                    if (qt * BQ + c0 + i < kj) e0 = 0.f;
+                                    if (qt * BQ + c0 + i + 1 < kj) e1 = 0.f;
+                                }
+                                const uint64_t t2 = ptx::add_f32x2(ptx::pack_f32x2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), nd[k]);
+                                float d0, d1;
+                                ptx::unpack_f32x2(ptx::mul_f32x2(ptx::pack_f32x2(e0, e1), t2), d0, d1);
+                                pp[k] = ptx::pack_bf16x2(e0, e1);
+                                dd[k] = ptx::pack_bf16x2(d0, d1);
                             }
-                            st_shared16(sw128_addr(ptb, BK, r, c + u * 8), pack8(p));
-                            st_shared16(sw128_addr(dstb, BK, r, c + u * 8), pack8(ds));
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) { pt[u * 4 + k] = pp[k]; dst[u * 4 + k] = dd[k]; }
                         }
-                    }
+                        // bf16 pairs over the first half of this thread's own score columns (the other thread of the row
+                        // owns the other 32 columns, so neither overwrites scores its partner has not read yet)
+                        ptx::tmem_st16(tmem + st * 128 + lane_addr + c0, pt);
+                        ptx::tmem_st16(tmem + st * 128 + kTmDP + lane_addr + c0, dst);
+                        ptx::tmem_st_wait();
+                    };
+                    if (diag) block(std::true_type{}); else block(std::false_type{});
+                    KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 5);
                     ptx::tc_fence_before();
-                    ptx::fence_proxy_async();
                     __syncwarp();
                     if (lane == 0) ptx::mbar_arrive(&t_full[st]);
+                    KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 6);
                 }
             }
             // epilogue of the item: dV, dK (scaled, inverse-rotated) -> d(qkv)
@@ -1146,12 +1192,18 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         const int q4 = warp & 3, half = (warp - 2) >> 2;
         const int r = q4 * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
+        const int c0 = half * 32;
+        uint32_t st_off[4];                                            // swizzled offsets of this thread's four 16-byte stores
+#pragma unroll
+        for (int u = 0; u < 4; ++u) st_off[u] = r * 128 + (((half * 4 + u) ^ (r & 7)) << 4);
+        const uint64_t scale2 = ptx::pack_f32x2(a.scale_log2, a.scale_log2);
         int item_it = 0, n_it = 0;
         for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
             int b, h, qt; decode(it, b, h, qt);
             const int qi = qt * BM + r;
             const int64_t so = ((int64_t)b * a.H + h) * a.S + qi;
             const float lse = a.lse[so], delta = a.delta[so];
+            const uint64_t nlse2 = ptx::pack_f32x2(-lse, -lse), ndel2 = ptx::pack_f32x2(-delta, -delta);
             const int nkv = (qt + 1) * (BM / BN);
             for (int j = 0; j < nkv; ++j, ++n_it) {
                 const int st = n_it & 1;
@@ -1160,25 +1212,35 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 ptx::tc_fence_after();
                 const bool diag = j * BN + BN > qt * BM;
                 const uint32_t dsb = ptx::smem_u32(sDS + st * kSBytes);
-                {
-                    const int c = half * 32;
+                // dS = exp2(S * scale - lse) * (dP - delta) on packed fp32 pairs (see attn_bwd_dkv_kernel)
+                auto block = [&](auto diag_c) {
+                    constexpr bool DIAG = decltype(diag_c)::value;
                     uint32_t sv[32], dv[32];
-                    ptx::tmem_ld32(tmem + st * 128 + lane_addr + c, sv);
-                    ptx::tmem_ld32(tmem + st * 128 + kTmDP + lane_addr + c, dv);
+                    ptx::tmem_ld32(tmem + st * 128 + lane_addr + c0, sv);
+                    ptx::tmem_ld32(tmem + st * 128 + kTmDP + lane_addr + c0, dv);
                     ptx::tmem_ld_wait();
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
-                        float ds[8];
+                        uint32_t dd[4];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int col = c + u * 8 + i;
-                            float e = exp2f(__uint_as_float(sv[u * 8 + i]) * a.scale_log2 - lse);
-                            if (diag && j * BN + col > qi) e = 0.f;
-                            ds[i] = e * (__uint_as_float(dv[u * 8 + i]) - delta);
+                        for (int k = 0; k < 4; ++k) {
+                            const int i = u * 8 + 2 * k;
+                            float x0, x1;
+                            ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), scale2, nlse2), x0, x1);
+                            float e0 = ptx::ex2(x0), e1 = ptx::ex2(x1);
+                            if (DIAG) {
+                                if (j * BN + c0 + i > qi) e0 = 0.f;
+                                if (j * BN + c0 + i + 1 > qi) e1 = 0.f;
+                            }
+                            const uint64_t t2 = ptx::add_f32x2(ptx::pack_f32x2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), ndel2);
+                            float d0, d1;
+                            ptx::unpack_f32x2(ptx::mul_f32x2(ptx::pack_f32x2(e0, e1), t2), d0, d1);
+                            dd[k] = ptx::pack_bf16x2(d0, d1);
                         }
-                        st_shared16(sw128_addr(dsb, BM, r, c + u * 8), pack8(ds));
+                        ptx::st_shared_v4(dsb + st_off[u], dd);
                     }
-                }
+                };
+                if (diag) block(std::true_type{}); else block(std::false_type{});
                 ptx::tc_fence_before();
                 ptx::fence_proxy_async();
                 __syncwarp();

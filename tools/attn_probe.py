@@ -20,7 +20,7 @@ LIB = os.path.join(ROOT, "build", "libattn_dbg.so")
 def build():
     os.makedirs(os.path.dirname(LIB), exist_ok=True)
     cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-           "--expt-relaxed-constexpr", "-DFTL_ATTN_DEBUG", "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
+           "--expt-relaxed-constexpr", "-DFTL_ATTN_DEBUG", *os.environ.get("FTL_PROBE_DEFS", "").split(), "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
            "-I", os.path.join(ROOT, "csrc"), "-I", os.path.join(ROOT, "include"),
            os.path.join(ROOT, "csrc", "attn_tc.cu"), "-o", LIB, "-lcuda"]
     subprocess.check_call(cmd)
@@ -60,5 +60,45 @@ def run():
     print("cycles per tile (steady state):", per)
 
 
+def run_bwd():
+    """Timeline of the first work unit of CTA 0 in attn_bwd_dkv_kernel (per 128-key x 64-query inner iteration)."""
+    import torch
+    B, S, H, KV, hd = 1, 2048, 32, 8, 128
+    lib = ctypes.CDLL(LIB)
+    torch.manual_seed(0)
+    W = (H + 2 * KV) * hd
+    qkv = (torch.randn(B * S, W, device="cuda") * 0.7).to(torch.bfloat16)
+    dout = (torch.randn(B * S, H * hd, device="cuda") * 0.5).to(torch.bfloat16)
+    out = torch.empty(B * S, H * hd, device="cuda", dtype=torch.bfloat16)
+    lse = torch.empty(B * H * S, device="cuda"); delta = torch.empty_like(lse)
+    dqkv = torch.zeros_like(qkv)
+    vp, i64, i32 = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int
+    st = torch.cuda.current_stream().cuda_stream
+    lib.ftl_attn_fwd.argtypes = [vp, i64, vp, i64, vp, i32, i32, i32, i32, i32, vp]
+    assert lib.ftl_attn_fwd(qkv.data_ptr(), qkv.stride(0), out.data_ptr(), out.stride(0), lse.data_ptr(), B, S, H, KV, hd, st) == 0
+    lib.ftl_attn_bwd_scratch_bytes.restype = i64
+    lib.ftl_attn_bwd_scratch_bytes.argtypes = [i32] * 5
+    scratch = torch.empty(max(lib.ftl_attn_bwd_scratch_bytes(B, S, H, KV, hd) // 4, 1), device="cuda")
+    lib.ftl_attn_bwd.argtypes = [vp, i64, vp, vp, i64, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
+    for _ in range(2):
+        rc = lib.ftl_attn_bwd(qkv.data_ptr(), qkv.stride(0), out.data_ptr(), dout.data_ptr(), out.stride(0), lse.data_ptr(),
+                              delta.data_ptr(), dqkv.data_ptr(), None, None, scratch.data_ptr(), B, S, H, KV, hd, st)
+        assert rc == 0, rc
+    torch.cuda.synchronize()
+    host = (ctypes.c_longlong * (64 * 16))()
+    lib.ftl_attn_dbg_read.argtypes = [vp]
+    assert lib.ftl_attn_dbg_read(host) == 0
+    which = sys.argv[2] if len(sys.argv) > 2 else "dkv"
+    names = {"dkv": ["top", "bar", "Srdy", "Tfree", "ld", "math", "pub", "-", "M.Qld", "M.top", "M.Tseen", "M.iss"],
+             "dq": ["top", "bar", "Srdy", "Tfree", "ld", "math", "pub", "-", "M.Kld", "M.top", "M.Tseen", "M.iss"]}[which]
+    t0 = min(host[k] for k in range(16) if host[k])
+    n = max(t for t in range(64) if host[t * 16]) + 1
+    print("iter " + " ".join(f"{x:>7}" for x in names))
+    for t in range(n):
+        print(f"{t:4d} " + " ".join(f"{host[t * 16 + k] - t0 if host[t * 16 + k] else -1:7d}" for k in range(len(names))))
+    if n > 6:
+        print("cycles per iteration (steady state):", (host[(n - 2) * 16] - host[2 * 16]) / (n - 4))
+
+
 if __name__ == "__main__":
-    build() if sys.argv[1] == "build" else run()
+    {"build": build, "run": run, "bwd": run_bwd}[sys.argv[1]]()
