@@ -89,6 +89,9 @@ struct AttnArgs {
     // units and leave fp32 partials in `partial`, which attn_dkv_reduce folds in chunk order (deterministic).
     int chunk_len, units;
     float* partial;                // [units][2][128][hd] fp32
+    const __nv_bfloat16* qkv_in;   // backward: the forward's fused projection and dO, read directly by the dQ kernel
+    const __nv_bfloat16* dout_in;
+    int64_t ld_do;
 };
 
 // unit -> (batch, kv head, key tile, inner range [n0, n1), whether the unit is the whole item)
@@ -1071,42 +1074,41 @@ attn_dkv_reduce_kernel(const AttnArgs a) {
 // ================================================================================================= backward: dQ
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
-attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmQKV64,
-                   const __grid_constant__ CUtensorMap tmDO, const AttnArgs a) {
+attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a) {
+    // Every A operand of this kernel lives in TMEM: Q and dO of the query tile (bf16, written once per item by the math
+    // threads straight from global memory) and dS (written over the first half of each thread's dP columns).  Shared
+    // memory then only carries the K / V ring, i.e. 48 KB of operand reads per key tile instead of 144 KB: the previous
+    // version, with Q, dO and dS in shared memory, was bound by shared-memory bandwidth (tools/umma_bench.cu: an SS
+    // 128x64x16 MMA takes 48 cycles, its TS form 32; and every st.shared / ld.shared of the math warps queued behind
+    // the tensor core's operand fetches).
     constexpr int BM = 128, BN = 64;                   // query tile (UMMA M), key tile (UMMA N)
-    constexpr int kQBytes = BM * HD * 2, kKBytes = BN * HD * 2, kSBytes = BM * BN * 2;
+    constexpr int kKBytes = BN * HD * 2;
     constexpr int kTmDP = 64, kTmDQ = 256;            // S / dP of buffer b at b*128 and b*128 + 64
-    constexpr int NK = 4;      // K / V stages: loads run ahead of the MMAs
+    constexpr int kTmQ = 384, kTmDO = 384 + HD / 2;   // bf16 A operands: HD/2 columns each
+    constexpr int NK = 6;      // K / V stages: loads run ahead of the MMAs
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sQ = smem;
-    uint8_t* sDO = sQ + kQBytes;
-    uint8_t* sK = sDO + kQBytes;                       // NK stages [BN x HD]
+    uint8_t* sK = smem;                                // NK stages [BN x HD]
     uint8_t* sV = sK + NK * kKBytes;                   // NK stages
-    uint8_t* sDS = sV + NK * kKBytes;                  // dS [BM x BN], 2 buffers
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + 2 * kSBytes);
-    uint64_t* q_full = bars;         // 1
-    uint64_t* q_empty = bars + 1;    // 1
-    uint64_t* kv_full = bars + 2;    // NK
-    uint64_t* kv_empty = bars + 6;   // NK
-    uint64_t* s_full = bars + 10;    // 2
-    uint64_t* t_full = bars + 12;    // 2
-    uint64_t* t_empty = bars + 14;   // 2
-    uint64_t* acc_full = bars + 16;  // 1
-    uint64_t* acc_empty = bars + 17; // 1
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + NK * kKBytes);
+    uint64_t* qd_full = bars;        // 1: Q, dO of the item are in TMEM (8 math warps)
+    uint64_t* kv_full = bars + 2;    // NK (<= 8)
+    uint64_t* kv_empty = bars + 10;  // NK
+    uint64_t* s_full = bars + 18;    // 2
+    uint64_t* t_full = bars + 20;    // 2
+    uint64_t* acc_full = bars + 22;  // 1
+    uint64_t* acc_empty = bars + 23; // 1
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q_tiles = a.S / BM, rep = a.H / a.KV;
     const int items = a.B * a.H * q_tiles;
 
     if (warp == 0 && lane == 0) {
-        ptx::prefetch_tmap(&tmQKV);
-        ptx::mbar_init(q_full, 1); ptx::mbar_init(q_empty, 1);
+        ptx::prefetch_tmap(&tmQKV64);
+        ptx::mbar_init(qd_full, 8);
         for (int i = 0; i < NK; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) {
-            ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&t_full[i], 8); ptx::mbar_init(&t_empty[i], 1);
-        }
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&t_full[i], 8); }
         ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_empty, 8);
         ptx::fence_barrier_init();
     }
@@ -1124,17 +1126,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
 
     if (warp == 0) {
         if (ptx::elect_one()) {
-            int item_it = 0, kv_it = 0;
-            for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
+            int kv_it = 0;
+            for (int it = blockIdx.x; it < items; it += gridDim.x) {
                 int b, h, qt; decode(it, b, h, qt);
-                const int g = h / rep, row0 = b * a.S + qt * BM;
-                ptx::mbar_wait(q_empty, (item_it & 1) ^ 1);
-                ptx::mbar_arrive_expect_tx(q_full, 2 * kQBytes);
-#pragma unroll
-                for (int c = 0; c < HD / 64; ++c) {
-                    ptx::tma_load_2d(sQ + c * BM * 128, &tmQKV, q_full, h * HD + c * 64, row0);
-                    ptx::tma_load_2d(sDO + c * BM * 128, &tmDO, q_full, h * HD + c * 64, row0);
-                }
+                const int g = h / rep;
                 const int nkv = (qt + 1) * (BM / BN);
                 for (int j = 0; j < nkv; ++j, ++kv_it) {
                     const int st = kv_it % NK;
@@ -1153,25 +1148,29 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(BM, BN, false, false);
         constexpr uint32_t idesc_q = ptx::umma_idesc_bf16(BM, HD, false, true);    // dQ = dS K, B = K MN-major
         int item_it = 0, n_it = 0;                                      // n_it: global key-tile counter
-        const uint32_t qa = ptx::smem_u32(sQ), doa = ptx::smem_u32(sDO);
         auto issue_sdp = [&](int t) {                                   // S, dP of tile t -> TMEM buffer t & 1
             const int st = t & 1, ks = t % NK;
             ptx::mbar_wait(&kv_full[ks], (t / NK) & 1);
             ptx::tc_fence_after();
             if (ptx::elect_one()) {
-                const uint32_t kb = ptx::smem_u32(sK + ks * kKBytes), vb = ptx::smem_u32(sV + ks * kKBytes);
-                umma_tile<HD / 16, BM, BN, false>(tmem + st * 128, qa, kb, idesc_s, false);
-                umma_tile<HD / 16, BM, BN, false>(tmem + st * 128 + kTmDP, doa, vb, idesc_s, false);
+                const uint64_t dk = desc_kmajor0(ptx::smem_u32(sK + ks * kKBytes)), dv = desc_kmajor0(ptx::smem_u32(sV + ks * kKBytes));
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    ptx::umma_bf16_ts(tmem + st * 128, tmem + kTmQ + k * 8, desc_kmajor_step(dk, BN, k), idesc_s, k != 0 ? 1u : 0u);
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    ptx::umma_bf16_ts(tmem + st * 128 + kTmDP, tmem + kTmDO + k * 8, desc_kmajor_step(dv, BN, k), idesc_s, k != 0 ? 1u : 0u);
                 ptx::umma_commit(&s_full[st]);
             }
             __syncwarp();
         };
         for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
             int b, h, qt; decode(it, b, h, qt);
-            ptx::mbar_wait(q_full, item_it & 1);
-            ptx::mbar_wait(acc_empty, (item_it & 1) ^ 1);
+            ptx::mbar_wait(qd_full, item_it & 1);
+            ptx::tc_fence_after();
             const int nkv = (qt + 1) * (BM / BN);
             issue_sdp(n_it);
+            ptx::mbar_wait(acc_empty, (item_it & 1) ^ 1);               // the epilogue of the previous item has read dQ
             for (int j = 0; j < nkv; ++j, ++n_it) {
                 if (j + 1 < nkv) issue_sdp(n_it + 1);
                 const int st = n_it & 1;
@@ -1179,11 +1178,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
                     const int ks = n_it % NK;
-                    const uint32_t dsa = ptx::smem_u32(sDS + st * kSBytes), kb = ptx::smem_u32(sK + ks * kKBytes);
-                    umma_tile<BN / 16, BM, BN, true>(tmem + kTmDQ, dsa, kb, idesc_q, j != 0);
-                    ptx::umma_commit(&t_empty[st]);
+                    // A = dS from TMEM: keys 0-31 of the tile sit in columns [0,16) of the dP buffer, keys 32-63 in [32,48)
+                    const uint64_t dkm = desc_mnmajor0(ptx::smem_u32(sK + ks * kKBytes), BN);
+#pragma unroll
+                    for (int k = 0; k < BN / 16; ++k)
+                        ptx::umma_bf16_ts(tmem + kTmDQ, tmem + st * 128 + kTmDP + (k >> 1) * 32 + (k & 1) * 8, desc_mnmajor_step(dkm, k), idesc_q,
+                                          (j != 0 || k != 0) ? 1u : 0u);
                     ptx::umma_commit(&kv_empty[ks]);
-                    if (j == nkv - 1) { ptx::umma_commit(acc_full); ptx::umma_commit(q_empty); }
+                    if (j == nkv - 1) ptx::umma_commit(acc_full);
                 }
                 __syncwarp();
             }
@@ -1193,11 +1195,34 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         const int r = q4 * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
         const int c0 = half * 32;
-        uint32_t st_off[4];                                            // swizzled offsets of this thread's four 16-byte stores
-#pragma unroll
-        for (int u = 0; u < 4; ++u) st_off[u] = r * 128 + (((half * 4 + u) ^ (r & 7)) << 4);
         const uint64_t scale2 = ptx::pack_f32x2(a.scale_log2, a.scale_log2);
+        // this thread's half of the Q and dO rows of an item: global -> registers -> TMEM (bf16 pairs, HD/4 columns each)
+        auto stage_rows = [&](int it2) {
+            int b2, h2, qt2; decode(it2, b2, h2, qt2);
+            const int64_t tok = (int64_t)b2 * a.S + qt2 * BM + r;
+            const uint4* qrow = reinterpret_cast<const uint4*>(a.qkv_in + tok * a.ld_qkv + h2 * HD + half * (HD / 2));
+            const uint4* drow = reinterpret_cast<const uint4*>(a.dout_in + tok * a.ld_do + h2 * HD + half * (HD / 2));
+            uint32_t vq[HD / 4], vd[HD / 4];
+#pragma unroll
+            for (int i = 0; i < HD / 16; ++i) {
+                const uint4 x = qrow[i], y = drow[i];
+                vq[4 * i] = x.x; vq[4 * i + 1] = x.y; vq[4 * i + 2] = x.z; vq[4 * i + 3] = x.w;
+                vd[4 * i] = y.x; vd[4 * i + 1] = y.y; vd[4 * i + 2] = y.z; vd[4 * i + 3] = y.w;
+            }
+            if constexpr (HD == 128) {
+                ptx::tmem_st32(tmem + kTmQ + lane_addr + half * (HD / 4), vq);
+                ptx::tmem_st32(tmem + kTmDO + lane_addr + half * (HD / 4), vd);
+            } else {
+                ptx::tmem_st16(tmem + kTmQ + lane_addr + half * (HD / 4), vq);
+                ptx::tmem_st16(tmem + kTmDO + lane_addr + half * (HD / 4), vd);
+            }
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(qd_full);
+        };
         int item_it = 0, n_it = 0;
+        if ((int)blockIdx.x < items) stage_rows(blockIdx.x);
         for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
             int b, h, qt; decode(it, b, h, qt);
             const int qi = qt * BM + r;
@@ -1208,46 +1233,41 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             for (int j = 0; j < nkv; ++j, ++n_it) {
                 const int st = n_it & 1;
                 ptx::mbar_wait(&s_full[st], (n_it >> 1) & 1);
-                ptx::mbar_wait(&t_empty[st], ((n_it >> 1) & 1) ^ 1);   // dQ MMA of tile n-2 no longer reads this dS buffer
                 ptx::tc_fence_after();
                 const bool diag = j * BN + BN > qt * BM;
-                const uint32_t dsb = ptx::smem_u32(sDS + st * kSBytes);
                 // dS = exp2(S * scale - lse) * (dP - delta) on packed fp32 pairs (see attn_bwd_dkv_kernel)
                 auto block = [&](auto diag_c) {
                     constexpr bool DIAG = decltype(diag_c)::value;
-                    uint32_t sv[32], dv[32];
+                    uint32_t sv[32], dv[32], dst[16];
                     ptx::tmem_ld32(tmem + st * 128 + lane_addr + c0, sv);
                     ptx::tmem_ld32(tmem + st * 128 + kTmDP + lane_addr + c0, dv);
                     ptx::tmem_ld_wait();
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        uint32_t dd[4];
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const int i = u * 8 + 2 * k;
-                            float x0, x1;
-                            ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), scale2, nlse2), x0, x1);
-                            float e0 = ptx::ex2(x0), e1 = ptx::ex2(x1);
-                            if (DIAG) {
-                                if (j * BN + c0 + i > qi) e0 = 0.f;
-                                if (j * BN + c0 + i + 1 > qi) e1 = 0.f;
-                            }
-                            const uint64_t t2 = ptx::add_f32x2(ptx::pack_f32x2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), ndel2);
-                            float d0, d1;
-                            ptx::unpack_f32x2(ptx::mul_f32x2(ptx::pack_f32x2(e0, e1), t2), d0, d1);
-                            dd[k] = ptx::pack_bf16x2(d0, d1);
+                    for (int i = 0; i < 32; i += 2) {
+                        float x0, x1;
+                        ptx::unpack_f32x2(ptx::fma_f32x2(ptx::pack_f32x2(__uint_as_float(sv[i]), __uint_as_float(sv[i + 1])), scale2, nlse2), x0, x1);
+                        float e0 = ptx::ex2(x0), e1 = ptx::ex2(x1);
+                        if (DIAG) {
+                            if (j * BN + c0 + i > qi) e0 = 0.f;
+                            if (j * BN + c0 + i + 1 > qi) e1 = 0.f;
                         }
-                        ptx::st_shared_v4(dsb + st_off[u], dd);
+                        const uint64_t t2 = ptx::add_f32x2(ptx::pack_f32x2(__uint_as_float(dv[i]), __uint_as_float(dv[i + 1])), ndel2);
+                        float d0, d1;
+                        ptx::unpack_f32x2(ptx::mul_f32x2(ptx::pack_f32x2(e0, e1), t2), d0, d1);
+                        dst[i >> 1] = ptx::pack_bf16x2(d0, d1);
                     }
+                    // bf16 pairs over the first half of this thread's own dP columns (its partner owns the other 32)
+                    ptx::tmem_st16(tmem + st * 128 + kTmDP + lane_addr + c0, dst);
+                    ptx::tmem_st_wait();
                 };
                 if (diag) block(std::true_type{}); else block(std::false_type{});
                 ptx::tc_fence_before();
-                ptx::fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&t_full[st]);
             }
-            ptx::mbar_wait(acc_full, item_it & 1);
+            ptx::mbar_wait(acc_full, item_it & 1);                       // every MMA of the item has completed
             ptx::tc_fence_after();
+            if (it + (int)gridDim.x < items) stage_rows(it + gridDim.x); // next Q, dO: S, dP of its first tile start under the epilogue
             __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD;
 #pragma unroll 1
             for (int c = half * (HD / 2); c < (half + 1) * (HD / 2); c += 32) {
@@ -1397,10 +1417,11 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
     a.scale = 1.f / sqrtf((float)hd); a.scale_log2 = a.scale * kLog2e;
     dkv_plan(B, S, H, KV, &a.chunk_len, &a.units);
     a.partial = scratch;
+    a.qkv_in = (const __nv_bfloat16*)qkv; a.dout_in = (const __nv_bfloat16*)d_out; a.ld_do = ld_out;
     const int items_kv = a.units, items_q = B * H * (S / 128), items_red = B * KV * (S / 128);
     if (hd == 128) {
         constexpr int smem_kv = 2 * 128 * 128 * 2 + 6 * 64 * 128 * 2 + 4 * 128 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
-        constexpr int smem_q = 2 * 128 * 128 * 2 + 8 * 64 * 128 * 2 + 2 * 128 * 64 * 2 + 1024 + 256;
+        constexpr int smem_q = 12 * 64 * 128 * 2 + 1024 + 256;                     // K / V ring only
         static bool once = false;
         if (!once) {
             if ((e = set_smem(attn_bwd_dkv_kernel<128>, smem_kv))) return e;
@@ -1411,10 +1432,10 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
         FTL_LAUNCH_CHECK();
         attn_dkv_reduce_kernel<128><<<items_red * 16, 128, 0, stream>>>(a);
         FTL_LAUNCH_CHECK();
-        attn_bwd_dq_kernel<128><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq128, tq64, tdo128, a);
+        attn_bwd_dq_kernel<128><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq64, a);
     } else {
         constexpr int smem_kv = 2 * 128 * 64 * 2 + 6 * 64 * 64 * 2 + 4 * 128 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
-        constexpr int smem_q = 2 * 128 * 64 * 2 + 8 * 64 * 64 * 2 + 2 * 128 * 64 * 2 + 1024 + 256;
+        constexpr int smem_q = 12 * 64 * 64 * 2 + 1024 + 256;
         static bool once = false;
         if (!once) {
             if ((e = set_smem(attn_bwd_dkv_kernel<64>, smem_kv))) return e;
@@ -1425,7 +1446,7 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
         FTL_LAUNCH_CHECK();
         attn_dkv_reduce_kernel<64><<<items_red * 16, 64, 0, stream>>>(a);
         FTL_LAUNCH_CHECK();
-        attn_bwd_dq_kernel<64><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq128, tq64, tdo128, a);
+        attn_bwd_dq_kernel<64><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq64, a);
     }
     return (int)cudaGetLastError();
 }
