@@ -1376,7 +1376,14 @@ static void dkv_plan(int B, int S, int H, int KV, int* chunk_len, int* units) {
     int64_t total = 0;
     for (int k = 0; k < kt_n; ++k) total += (int64_t)rep * (q64 - 2 * k);
     total *= (int64_t)B * KV;
-    int lc = (int)((total + 4 * kNumSMs - 1) / (4 * kNumSMs));
+    // Units per SM: every unit pays a fill/drain of the MMA pipeline and, when an item is split, 128 KB of fp32
+    // partials; short problems (model shape: 59 inner iterations per SM) run best with 2 long units per SM, long ones
+    // (seq 8192: 900 per SM) balance better with 6.  Measured: profiles/attn_tc_notes.md.
+    static const int forced = [] { const char* v = getenv("FTL_DKV_UNITS_PER_SM"); return v ? atoi(v) : 0; }();
+    int per_sm = (int)(total / kNumSMs / 30);
+    per_sm = per_sm < 2 ? 2 : per_sm > 6 ? 6 : per_sm;
+    if (forced > 0) per_sm = forced;
+    int lc = (int)((total + per_sm * kNumSMs - 1) / (per_sm * kNumSMs));
     if (lc < 8) lc = 8;
     int u = 0;
     for (int k = 0; k < kt_n; ++k) u += (rep * (q64 - 2 * k) + lc - 1) / lc;

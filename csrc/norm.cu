@@ -62,7 +62,8 @@ rmsnorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
 }
 
 // dx = rstd * (dy*w - xhat * mean(dy*w*xhat)) [+ dres];  dw_partial[cta] = sum_rows dy * bf16(xhat)
-template <bool kAddRes>
+// kVec = vectors of 8 bf16 per thread (1, 2 or 4): sized to the row so that dim 4096 with 256 threads keeps two CTAs per SM
+template <bool kAddRes, int kVec>
 __global__ void __launch_bounds__(256)
 rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                    const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd_in,
@@ -70,26 +71,47 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
                    float* __restrict__ dw_partial, int rows, int dim) {
     __shared__ float red[33];
     const int nvec = dim >> 3;
-    float dw_acc[kNormMaxVec][8];
-    float wreg[kNormMaxVec][8];
+    float dw_acc[kVec][8];
+    float wreg[kVec][8];
 #pragma unroll
-    for (int k = 0; k < kNormMaxVec; ++k) {
+    for (int k = 0; k < kVec; ++k) {
         const int i = threadIdx.x + k * blockDim.x;
 #pragma unroll
         for (int j = 0; j < 8; ++j) dw_acc[k][j] = 0.f;
         if (i < nvec) unpack8(ld8(w + i * 8), wreg[k]);
     }
+    // A CTA walks its rows one after the other with a block reduction in the middle of each, so per row the chain used
+    // to be load latency -> reduce -> residual load latency -> store.  All three inputs of a row are now requested at
+    // once and the NEXT row's are requested before the current row's reduction, which keeps ~2 rows of loads in flight
+    // per CTA (the kernel is HBM-bound: 3 reads + 1 write of [rows, dim] bf16).
+    bf16x8 nx[kVec], ndy[kVec], nres[kVec];
+    float nrstd = 0.f;
+    auto fetch = [&](int64_t row) {
+        nrstd = rstd_in[row];
+#pragma unroll
+        for (int k = 0; k < kVec; ++k) {
+            const int i = threadIdx.x + k * blockDim.x;
+            if (i < nvec) {
+                nx[k] = ld8(x + row * dim + i * 8);
+                ndy[k] = ld8(dy + row * dim + i * 8);
+                if (kAddRes) nres[k] = ld8(dres + row * dim + i * 8);
+            }
+        }
+    };
+    if ((int64_t)blockIdx.x < rows) fetch(blockIdx.x);
     for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
-        const float rstd = rstd_in[row];
-        float xh[kNormMaxVec][8], dyw[kNormMaxVec][8];
+        const float rstd = nrstd;
+        float xh[kVec][8], dyw[kVec][8];
+        bf16x8 res[kVec];
         float dot = 0.f;
 #pragma unroll
-        for (int k = 0; k < kNormMaxVec; ++k) {
+        for (int k = 0; k < kVec; ++k) {
             const int i = threadIdx.x + k * blockDim.x;
             if (i < nvec) {
                 float d[8];
-                unpack8(ld8(x + row * dim + i * 8), xh[k]);
-                unpack8(ld8(dy + row * dim + i * 8), d);
+                unpack8(nx[k], xh[k]);
+                unpack8(ndy[k], d);
+                if (kAddRes) res[k] = nres[k];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     xh[k][j] *= rstd;
@@ -99,9 +121,10 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
                 }
             }
         }
+        if (row + gridDim.x < rows) fetch(row + gridDim.x);
         const float mean = block_sum(dot, red) / (float)dim;
 #pragma unroll
-        for (int k = 0; k < kNormMaxVec; ++k) {
+        for (int k = 0; k < kVec; ++k) {
             const int i = threadIdx.x + k * blockDim.x;
             if (i < nvec) {
                 float o[8];
@@ -109,7 +132,7 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
                 for (int j = 0; j < 8; ++j) o[j] = rstd * (dyw[k][j] - xh[k][j] * mean);
                 if (kAddRes) {
                     float r[8];
-                    unpack8(ld8(dres + row * dim + i * 8), r);
+                    unpack8(res[k], r);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) o[j] += r[j];
                 }
@@ -119,7 +142,7 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
     }
     float* out = dw_partial + (int64_t)blockIdx.x * dim;
 #pragma unroll
-    for (int k = 0; k < kNormMaxVec; ++k) {
+    for (int k = 0; k < kVec; ++k) {
         const int i = threadIdx.x + k * blockDim.x;
         if (i < nvec) {
             *reinterpret_cast<float4*>(out + i * 8) = make_float4(dw_acc[k][0], dw_acc[k][1], dw_acc[k][2], dw_acc[k][3]);
@@ -157,6 +180,22 @@ static inline int norm_threads(int dim) {
     return t;
 }
 
+// picks the instantiation with the fewest vectors per thread that covers the row
+static void launch_rmsnorm_bwd(int parts, int threads, cudaStream_t stream, const __nv_bfloat16* DY, const __nv_bfloat16* X,
+                               const __nv_bfloat16* W, const float* rstd, const __nv_bfloat16* DR, __nv_bfloat16* DX,
+                               float* scratch, int rows, int dim) {
+    const int vec = (dim / 8 + threads - 1) / threads;
+#define FTL_RMS_BWD(V)                                                                                             \
+    do {                                                                                                           \
+        if (DR) rmsnorm_bwd_kernel<true, V><<<parts, threads, 0, stream>>>(DY, X, W, rstd, DR, DX, scratch, rows, dim); \
+        else rmsnorm_bwd_kernel<false, V><<<parts, threads, 0, stream>>>(DY, X, W, rstd, nullptr, DX, scratch, rows, dim); \
+    } while (0)
+    if (vec <= 1) FTL_RMS_BWD(1);
+    else if (vec <= 2) FTL_RMS_BWD(2);
+    else FTL_RMS_BWD(4);
+#undef FTL_RMS_BWD
+}
+
 }  // namespace ftl
 
 using namespace ftl;
@@ -184,8 +223,7 @@ FTL_API int ftl_rmsnorm_bwd(const void* dy, const void* x, const void* w, const 
     const int parts = ftl_rmsnorm_partials(rows);
     auto DY = (const __nv_bfloat16*)dy; auto X = (const __nv_bfloat16*)x; auto W = (const __nv_bfloat16*)w;
     auto DR = (const __nv_bfloat16*)dres; auto DX = (__nv_bfloat16*)dx;
-    if (dres) rmsnorm_bwd_kernel<true><<<parts, threads, 0, stream>>>(DY, X, W, rstd, DR, DX, scratch, rows, dim);
-    else rmsnorm_bwd_kernel<false><<<parts, threads, 0, stream>>>(DY, X, W, rstd, nullptr, DX, scratch, rows, dim);
+    launch_rmsnorm_bwd(parts, threads, stream, DY, X, W, rstd, DR, DX, scratch, rows, dim);
     FTL_LAUNCH_CHECK();
     rmsnorm_dw_finalize_kernel<<<(dim + 31) / 32, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw);
     FTL_LAUNCH_CHECK();
@@ -273,8 +311,7 @@ FTL_API int ftl_rmsnorm_bwd_static(const void* dy, const void* x, const void* w,
     if (threads > 256) threads = 256;
     auto DY = (const __nv_bfloat16*)dy; auto X = (const __nv_bfloat16*)x; auto W = (const __nv_bfloat16*)w;
     auto DR = (const __nv_bfloat16*)dres; auto DX = (__nv_bfloat16*)dx;
-    if (dres) rmsnorm_bwd_kernel<true><<<parts, threads, 0, stream>>>(DY, X, W, rstd, DR, DX, scratch, rows, dim);
-    else rmsnorm_bwd_kernel<false><<<parts, threads, 0, stream>>>(DY, X, W, rstd, nullptr, DX, scratch, rows, dim);
+    launch_rmsnorm_bwd(parts, threads, stream, DY, X, W, rstd, DR, DX, scratch, rows, dim);
     e = cudaGetLastError();
     if (e == cudaSuccess) {
         rmsnorm_dw_finalize_kernel<<<(dim + 31) / 32, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw);
