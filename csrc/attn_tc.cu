@@ -753,24 +753,33 @@ __device__ __forceinline__ void unrope8(float (&f)[8], const AttnArgs& a, int po
     }
 }
 
+// Work queues of the two backward kernels (same scheme as g_fwd2_sched): [0..1] dK/dV units, [2..3] dQ items.
+// The last CTA to see the end of a queue resets it, so launches must be stream-ordered per device (they are).
+__device__ int g_bwd_sched[4];
+__device__ __forceinline__ void sched_done(int* q) {
+    __threadfence();
+    if (atomicAdd(q + 1, 1) == (int)gridDim.x - 1) {
+        q[0] = 0; q[1] = 0;
+        __threadfence();
+    }
+}
+
 // ================================================================================================= backward: dK, dV
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmQKV64,
                     const __grid_constant__ CUtensorMap tmDO64, const AttnArgs a) {
     constexpr int BK = 128, BQ = 64;                   // key tile (UMMA M), query tile (UMMA N)
-    constexpr int kKBytes = BK * HD * 2, kQBytes = BQ * HD * 2, kTBytes = BK * BQ * 2;
+    constexpr int kKBytes = BK * HD * 2, kQBytes = BQ * HD * 2;
     constexpr int kTmDP = 64, kTmDV = 256, kTmDK = 256 + HD;   // S / dP of buffer b at b*128 and b*128 + 64
-    constexpr int NQ = 3;      // Q / dO stages: the TMA loads run two iterations ahead of the MMAs that consume them
+    constexpr int NQ = 4;      // Q / dO stages: the TMA loads run three iterations ahead of the MMAs that consume them
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem;
     uint8_t* sV = sK + kKBytes;
     uint8_t* sQ = sV + kKBytes;                        // NQ stages of [BQ x HD]
     uint8_t* sDO = sQ + NQ * kQBytes;                  // NQ stages
-    uint8_t* sPT = sDO + NQ * kQBytes;                 // P^T  [BK x BQ], 2 buffers
-    uint8_t* sDST = sPT + 2 * kTBytes;                 // dS^T [BK x BQ], 2 buffers
-    float* sLse = reinterpret_cast<float*>(sDST + 2 * kTBytes);   // 2 x BQ
+    float* sLse = reinterpret_cast<float*>(sDO + NQ * kQBytes);   // 2 x BQ (P^T and dS^T live in TMEM, not here)
     float* sDelta = sLse + 2 * BQ;                            // 2 x BQ
     uint64_t* bars = reinterpret_cast<uint64_t*>(sDelta + 2 * BQ);
     uint64_t* kv_full = bars;        // 1
@@ -778,11 +787,11 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     uint64_t* q_full = bars + 2;     // NQ (<= 4)
     uint64_t* q_empty = bars + 6;    // NQ
     uint64_t* s_full = bars + 10;    // 2  (S^T and dP^T of buffer b ready)
-    uint64_t* t_full = bars + 12;    // 2  (P^T, dS^T of buffer b in smem; its S/dP TMEM read)
-    uint64_t* t_empty = bars + 14;   // 2  (dV/dK MMAs that read buffer b have retired)
+    uint64_t* t_full = bars + 12;    // 2  (P^T, dS^T of buffer b written over its S^T / dP^T in TMEM)
     uint64_t* acc_full = bars + 16;  // 1
     uint64_t* acc_empty = bars + 17; // 1
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
+    int* sItem = reinterpret_cast<int*>(bars + 19);    // [2] unit handed out by the scheduler, published with kv_full
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k_tiles = a.S / BK, rep = a.H / a.KV;
@@ -793,7 +802,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
         ptx::mbar_init(kv_full, 1); ptx::mbar_init(kv_empty, 1);
         for (int i = 0; i < NQ; ++i) { ptx::mbar_init(&q_full[i], 1); ptx::mbar_init(&q_empty[i], 1); }
         for (int i = 0; i < 2; ++i) {
-            ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&t_full[i], 8); ptx::mbar_init(&t_empty[i], 1);
+            ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&t_full[i], 8);
         }
         ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_empty, 8);
         ptx::fence_barrier_init();
@@ -809,11 +818,17 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
 
     if (warp == 0) {
         if (ptx::elect_one()) {
-            int item_it = 0, q_it = 0;
-            for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
+            // Units are handed out by an atomic counter, longest first: with a static round-robin some CTAs drew three
+            // units and others two (ncu: SMs idle for a third of the kernel).  The unit index travels to the other
+            // warps through sItem, published by the arrival on kv_full.
+            int q_it = 0;
+            for (int item_it = 0;; ++item_it) {
+                const int it = atomicAdd(&g_bwd_sched[0], 1);
+                ptx::mbar_wait(kv_empty, (item_it & 1) ^ 1);
+                if (it >= items) { sItem[item_it & 1] = -1; ptx::mbar_arrive(kv_full); break; }
+                sItem[item_it & 1] = it;
                 int b, g, kt, n0, n1; bool whole;
                 dkv_decode(a, it, rep, q_tiles64, k_tiles, b, g, kt, n0, n1, whole);
-                ptx::mbar_wait(kv_empty, (item_it & 1) ^ 1);
                 ptx::mbar_arrive_expect_tx(kv_full, 2 * kKBytes);
                 const int krow = b * a.S + kt * BK;
 #pragma unroll
@@ -837,6 +852,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     }
                 }
             }
+            sched_done(&g_bwd_sched[0]);
         }
     } else if (warp == 1) {
         constexpr uint32_t idesc_st = ptx::umma_idesc_bf16(BK, BQ, false, false);   // S^T = K Q^T, dP^T = V dO^T
@@ -857,10 +873,12 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             }
             __syncwarp();
         };
-        for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
+        for (;; ++item_it) {
+            ptx::mbar_wait(kv_full, item_it & 1);
+            const int it = sItem[item_it & 1];
+            if (it < 0) break;
             int b, g, kt, n0, n1; bool whole;
             dkv_decode(a, it, rep, q_tiles64, k_tiles, b, g, kt, n0, n1, whole);
-            ptx::mbar_wait(kv_full, item_it & 1);
             ptx::mbar_wait(acc_empty, (item_it & 1) ^ 1);
             const int inner = n1 - n0;
             issue_sdp(n_it);
@@ -884,7 +902,6 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     for (int k = 0; k < BQ / 16; ++k)
                         ptx::umma_bf16_ts(tmem + kTmDK, tmem + st * 128 + kTmDP + (k >> 1) * 32 + (k & 1) * 8, desc_mnmajor_step(d_q, k), idesc_acc,
                                           (n != 0 || k != 0) ? 1u : 0u);
-                    ptx::umma_commit(&t_empty[st]);
                     ptx::umma_commit(&q_empty[qs]);
                     if (n == inner - 1) { ptx::umma_commit(acc_full); ptx::umma_commit(kv_empty); }
                 }
@@ -904,7 +921,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
         for (int u = 0; u < 4; ++u) st_off[u] = r * 128 + (((half * 4 + u) ^ (r & 7)) << 4);
         const uint64_t scale2 = ptx::pack_f32x2(a.scale_log2, a.scale_log2);
         int item_it = 0, n_it = 0;
-        for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
+        for (;; ++item_it) {
+            ptx::mbar_wait(kv_full, item_it & 1);
+            const int it = sItem[item_it & 1];
+            if (it < 0) break;
             int b, g, kt, n0, n1; bool whole;
             dkv_decode(a, it, rep, q_tiles64, k_tiles, b, g, kt, n0, n1, whole);
             const int kj = kt * BK + r;
@@ -934,7 +954,6 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     const int st = n_it & 1;
                     ptx::mbar_wait(&s_full[st], (n_it >> 1) & 1);
                     KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 2);
-                    ptx::mbar_wait(&t_empty[st], ((n_it >> 1) & 1) ^ 1);   // dV/dK of iteration n-2 no longer read this buffer
                     ptx::tc_fence_after();
                     KV_DBG(item_it == 0 && threadIdx.x == 64, n - n0, 3);
                     const bool diag = qt * BQ < kt * BK + BK;          // tile touches the diagonal: mask q < key
@@ -1098,7 +1117,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
     uint64_t* t_full = bars + 20;    // 2
     uint64_t* acc_full = bars + 22;  // 1
     uint64_t* acc_empty = bars + 23; // 1
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+    uint64_t* item_full = bars + 24; // 2: the scheduler's next item is in sItem[slot]
+    uint64_t* item_empty = bars + 26;// 2: MMA warp + 8 math warps have read it
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 28);
+    int* sItem = reinterpret_cast<int*>(bars + 29);    // [2]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q_tiles = a.S / BM, rep = a.H / a.KV;
@@ -1108,7 +1130,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
         ptx::prefetch_tmap(&tmQKV64);
         ptx::mbar_init(qd_full, 8);
         for (int i = 0; i < NK; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&t_full[i], 8); }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&t_full[i], 8);
+            ptx::mbar_init(&item_full[i], 1); ptx::mbar_init(&item_empty[i], 9);
+        }
         ptx::mbar_init(acc_full, 1); ptx::mbar_init(acc_empty, 8);
         ptx::fence_barrier_init();
     }
@@ -1126,8 +1151,16 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
 
     if (warp == 0) {
         if (ptx::elect_one()) {
+            // items come from an atomic counter, heaviest (latest query tiles) first: a static round-robin gave the
+            // first CTAs 76 key tiles and the last ones 44 (ncu: SMs idle for 23% of the kernel)
             int kv_it = 0;
-            for (int it = blockIdx.x; it < items; it += gridDim.x) {
+            for (int item_it = 0;; ++item_it) {
+                const int it = atomicAdd(&g_bwd_sched[2], 1);
+                const int sl = item_it & 1;
+                ptx::mbar_wait(&item_empty[sl], ((item_it >> 1) & 1) ^ 1);
+                sItem[sl] = it < items ? it : -1;
+                ptx::mbar_arrive(&item_full[sl]);
+                if (it >= items) break;
                 int b, h, qt; decode(it, b, h, qt);
                 const int g = h / rep;
                 const int nkv = (qt + 1) * (BM / BN);
@@ -1143,6 +1176,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
                     }
                 }
             }
+            sched_done(&g_bwd_sched[2]);
         }
     } else if (warp == 1) {
         constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(BM, BN, false, false);
@@ -1164,7 +1198,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
             }
             __syncwarp();
         };
-        for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
+        for (;; ++item_it) {
+            const int sl = item_it & 1;
+            ptx::mbar_wait(&item_full[sl], (item_it >> 1) & 1);
+            const int it = sItem[sl];
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&item_empty[sl]);
+            if (it < 0) break;
             int b, h, qt; decode(it, b, h, qt);
             ptx::mbar_wait(qd_full, item_it & 1);
             ptx::tc_fence_after();
@@ -1222,8 +1262,17 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
             if (lane == 0) ptx::mbar_arrive(qd_full);
         };
         int item_it = 0, n_it = 0;
-        if ((int)blockIdx.x < items) stage_rows(blockIdx.x);
-        for (int it = blockIdx.x; it < items; it += gridDim.x, ++item_it) {
+        auto next_item = [&](int idx) {                                // idx-th item of this CTA (-1: queue drained)
+            const int sl = idx & 1;
+            ptx::mbar_wait(&item_full[sl], (idx >> 1) & 1);
+            const int v = sItem[sl];
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&item_empty[sl]);
+            return v;
+        };
+        int it = next_item(0);
+        if (it >= 0) stage_rows(it);
+        for (; it >= 0; ++item_it) {
             int b, h, qt; decode(it, b, h, qt);
             const int qi = qt * BM + r;
             const int64_t so = ((int64_t)b * a.H + h) * a.S + qi;
@@ -1267,7 +1316,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
             }
             ptx::mbar_wait(acc_full, item_it & 1);                       // every MMA of the item has completed
             ptx::tc_fence_after();
-            if (it + (int)gridDim.x < items) stage_rows(it + gridDim.x); // next Q, dO: S, dP of its first tile start under the epilogue
+            const int it_next = next_item(item_it + 1);
+            if (it_next >= 0) stage_rows(it_next);                       // next Q, dO: S, dP of its first tile start under the epilogue
             __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD;
 #pragma unroll 1
             for (int c = half * (HD / 2); c < (half + 1) * (HD / 2); c += 32) {
@@ -1286,6 +1336,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(acc_empty);
+            it = it_next;
         }
     }
     ptx::tc_fence_before();
@@ -1377,11 +1428,11 @@ static void dkv_plan(int B, int S, int H, int KV, int* chunk_len, int* units) {
     for (int k = 0; k < kt_n; ++k) total += (int64_t)rep * (q64 - 2 * k);
     total *= (int64_t)B * KV;
     // Units per SM: every unit pays a fill/drain of the MMA pipeline and, when an item is split, 128 KB of fp32
-    // partials; short problems (model shape: 59 inner iterations per SM) run best with 2 long units per SM, long ones
-    // (seq 8192: 900 per SM) balance better with 6.  Measured: profiles/attn_tc_notes.md.
+    // partials; units are handed out dynamically (longest first), so a few long units per SM already balance.
+    // Measured (profiles/attn_tc_notes.md): 2 per SM is best at the model shape (59 inner iterations per SM),
+    // 3 at seq 8192 (900 per SM).
     static const int forced = [] { const char* v = getenv("FTL_DKV_UNITS_PER_SM"); return v ? atoi(v) : 0; }();
-    int per_sm = (int)(total / kNumSMs / 30);
-    per_sm = per_sm < 2 ? 2 : per_sm > 6 ? 6 : per_sm;
+    int per_sm = total / kNumSMs >= 256 ? 3 : 2;
     if (forced > 0) per_sm = forced;
     int lc = (int)((total + per_sm * kNumSMs - 1) / (per_sm * kNumSMs));
     if (lc < 8) lc = 8;
@@ -1427,7 +1478,7 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
     a.qkv_in = (const __nv_bfloat16*)qkv; a.dout_in = (const __nv_bfloat16*)d_out; a.ld_do = ld_out;
     const int items_kv = a.units, items_q = B * H * (S / 128), items_red = B * KV * (S / 128);
     if (hd == 128) {
-        constexpr int smem_kv = 2 * 128 * 128 * 2 + 6 * 64 * 128 * 2 + 4 * 128 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
+        constexpr int smem_kv = 2 * 128 * 128 * 2 + 8 * 64 * 128 * 2 + 4 * 64 * 4 + 1024 + 256;   // K, V, 4 x (Q, dO)
         constexpr int smem_q = 12 * 64 * 128 * 2 + 1024 + 256;                     // K / V ring only
         static bool once = false;
         if (!once) {
@@ -1441,7 +1492,7 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
         FTL_LAUNCH_CHECK();
         attn_bwd_dq_kernel<128><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq64, a);
     } else {
-        constexpr int smem_kv = 2 * 128 * 64 * 2 + 6 * 64 * 64 * 2 + 4 * 128 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
+        constexpr int smem_kv = 2 * 128 * 64 * 2 + 8 * 64 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
         constexpr int smem_q = 12 * 64 * 64 * 2 + 1024 + 256;
         static bool once = false;
         if (!once) {
