@@ -142,6 +142,7 @@ dp_adamw_allgather_kernel(__nv_bfloat16* const* __restrict__ peer_p, const __nv_
     const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4];
     const float bc1 = hyper[5], bc2_sqrt = hyper[6], coef = stats[1];
     const float step_size = lr / bc1, decay = 1.f - lr * wd;
+    const float vcut = adam_vcut(eps, bc2_sqrt);
     __nv_bfloat16* dst[W];
 #pragma unroll
     for (int r = 0; r < W; ++r) dst[r] = peer_p[r] + lo_vec * 8;
@@ -158,8 +159,8 @@ dp_adamw_allgather_kernel(__nv_bfloat16* const* __restrict__ peer_p, const __nv_
             const float gr = gf[j] * coef;
             mf[j] = mf[j] + (1.f - b1) * (gr - mf[j]);
             vf[j] = b2 * vf[j] + (1.f - b2) * gr * gr;
-            const float denom = sqrtf(vf[j]) / bc2_sqrt + eps;
-            pf[j] = pf[j] * decay - step_size * (mf[j] / denom);
+            const float denom = adam_denom(vf[j], bc2_sqrt, eps, vcut);
+            pf[j] = pf[j] * decay - step_size * adam_quot(mf[j], denom);
         }
         const bf16x8 np = pack8(pf);
         st8_stream(m + i * 8, pack8(mf));
@@ -196,6 +197,7 @@ adamw_shard_kernel(__nv_bfloat16* __restrict__ p, const __nv_bfloat16* __restric
     const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4];
     const float bc1 = hyper[5], bc2_sqrt = hyper[6], coef = stats[1];
     const float step_size = lr / bc1, decay = 1.f - lr * wd;
+    const float vcut = adam_vcut(eps, bc2_sqrt);
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
         float pf[8], gf[8], mf[8], vf[8];
         unpack8(ld8_stream(p + i * 8), pf);
@@ -207,8 +209,8 @@ adamw_shard_kernel(__nv_bfloat16* __restrict__ p, const __nv_bfloat16* __restric
             const float gr = gf[j] * coef;
             mf[j] = mf[j] + (1.f - b1) * (gr - mf[j]);
             vf[j] = b2 * vf[j] + (1.f - b2) * gr * gr;
-            const float denom = sqrtf(vf[j]) / bc2_sqrt + eps;
-            pf[j] = pf[j] * decay - step_size * (mf[j] / denom);
+            const float denom = adam_denom(vf[j], bc2_sqrt, eps, vcut);
+            pf[j] = pf[j] * decay - step_size * adam_quot(mf[j], denom);
         }
         st8_stream(p + i * 8, pack8(pf));
         st8_stream(m + i * 8, pack8(mf));

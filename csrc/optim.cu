@@ -81,6 +81,7 @@ adamw_kernel(__nv_bfloat16* __restrict__ p, const __nv_bfloat16* __restrict__ g,
     if (stats && stats[2] == 0.f) return;  // non-finite gradient norm: leave the state untouched
     const float step_size = lr / bc1;
     const float decay = 1.f - lr * wd;
+    const float vcut = adam_vcut(eps, bc2_sqrt);
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
         float pf[8], gf[8], mf[8], vf[8];
         unpack8(ld8_stream(p + i * 8), pf);
@@ -92,8 +93,8 @@ adamw_kernel(__nv_bfloat16* __restrict__ p, const __nv_bfloat16* __restrict__ g,
             const float gr = gf[j] * coef;
             mf[j] = mf[j] + (1.f - b1) * (gr - mf[j]);           // lerp(m, g, 1-b1)
             vf[j] = b2 * vf[j] + (1.f - b2) * gr * gr;
-            const float denom = sqrtf(vf[j]) / bc2_sqrt + eps;
-            pf[j] = pf[j] * decay - step_size * (mf[j] / denom);
+            const float denom = adam_denom(vf[j], bc2_sqrt, eps, vcut);
+            pf[j] = pf[j] * decay - step_size * adam_quot(mf[j], denom);
         }
         st8_stream(p + i * 8, pack8(pf));
         st8_stream(m + i * 8, pack8(mf));

@@ -33,6 +33,9 @@ from .symm import SymmetricBuffers
 class PipelinedTrainer(NativeTrainer):
     RS_CTAS = int(os.environ.get("FTL_RS_CTAS", "96"))       # SMs' worth of CTAs lent to phase 1 while GEMMs run
     UPD_CTAS = int(os.environ.get("FTL_UPD_CTAS", "0"))      # ... and to phase 2 (0 = 4 CTAs per SM: HBM-bound)
+    # The embedding bucket's gradients are the last ones of the backward: nothing else runs while its phase 1 (1 GB at
+    # W = 1) delays the norm, the first AdamW launch and with them the next forward, so it gets the whole GPU.
+    RS_LAST_CTAS = int(os.environ.get("FTL_RS_LAST_CTAS", "0"))
 
     # ---- state ---------------------------------------------------------------------------------------------------
     def _make_flat_state(self) -> FlatState:
@@ -53,7 +56,7 @@ class PipelinedTrainer(NativeTrainer):
         self.buckets: List[Tuple[int, int]] = [(starts[i], starts[i + 1]) for i in range(L + 2)]
         self.ranges = self._owned_ranges(flat)        # per bucket: flat ranges (lo, hi) this rank reduces and updates
         NB = len(self.buckets)
-        self.parts = N.dp_partials(self.RS_CTAS)
+        self.parts = max(N.dp_partials(self.RS_CTAS), N.dp_partials(self.RS_LAST_CTAS))
         self.range_slot, k = [], 0                    # index of each range's partial-sum slice
         for rs in self.ranges:
             self.range_slot.append(list(range(k, k + len(rs))))
@@ -114,7 +117,7 @@ class PipelinedTrainer(NativeTrainer):
             for (a, e), k in zip(self.ranges[b], self.range_slot[b]):
                 part = self.rs_partials[k * self.parts:(k + 1) * self.parts]
                 N.dp_reduce_scatter(self.symm.table("g"), self.env.rank, self.env.world_size, a, e - a, part,
-                                    self.comm_status, max_ctas=self.RS_CTAS)
+                                    self.comm_status, max_ctas=self.RS_LAST_CTAS if b == 0 else self.RS_CTAS)
 
     # ---- step pieces ---------------------------------------------------------------------------------------------
     def _begin_step(self, hyper: torch.Tensor) -> None:

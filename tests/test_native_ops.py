@@ -157,6 +157,19 @@ def test_grad_norm_and_adamw_match_torch(N):
     assert float(stats[2]) == 0.0 and torch.equal(p, before)
 
 
+def test_adamw_untouched_rows_exact(N):
+    """Elements with g = m = v = 0 (embedding rows no batch has touched) only see the weight decay: the clamp that keeps
+    sqrtf() off its zero/subnormal slow path (adam_vmin, csrc/common/util.cuh) must not change a bit of the result."""
+    n = 1 << 16
+    p = bf(n, seed=3)
+    g, m, v = torch.zeros_like(p), torch.zeros_like(p), torch.zeros_like(p)
+    v[: n // 2] = 1e-38                                   # tiny but non-zero second moments: below the clamp as well
+    hyper = torch.tensor([1e-2, 0.9, 0.999, 1e-8, 1e-2, 1 - 0.9, math.sqrt(1 - 0.999), 1.0], device=DEV)
+    want = (p.float() * (1.0 - 1e-2 * 1e-2)).to(torch.bfloat16)
+    N.adamw_step(p, g, m, v, hyper, None)
+    assert torch.equal(p, want) and not m.any()
+
+
 # ---- tcgen05 GEMMs (csrc/gemm_tc.cu): every operand-major combination and fused epilogue vs fp32 matmul ----
 def _rel(out, ref):
     return float((out.float() - ref).norm() / ref.norm())

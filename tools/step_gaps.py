@@ -49,3 +49,27 @@ for lo, hi in ((0, 2), (2, 5), (5, 10), (10, 50), (50, 200), (200, 1e9)):
 print("\n| gap us | after | before |\n|---:|---|---|")
 for gdur, x, y in sorted(gaps, key=lambda t: -t[0])[:24]:
     print(f"| {gdur:.0f} | `{x}` | `{y}` |")
+
+# what the other streams were doing during the largest gap (the step boundary)
+gi = max(range(len(ks) - 1), key=lambda i: ks[i + 1]["ts"] - (ks[i]["ts"] + ks[i]["dur"]))
+g0, g1 = ks[gi]["ts"] + ks[gi]["dur"], ks[gi + 1]["ts"]
+print(f"\nOther-stream kernels overlapping the largest gap ({(g1 - g0):.0f} us; times relative to its start):\n")
+print("| start us | dur us | kernel |\n|---:|---:|---|")
+for e in sorted(ev, key=lambda e: e["ts"]):
+    if e["args"].get("stream") != main and e["ts"] + e["dur"] > g0 - 500 and e["ts"] < g1:
+        print(f"| {e['ts'] - g0:.0f} | {e['dur']:.0f} | `{e['name'][:60]}` |")
+
+for pat in ("dp_adamw_allgather", "dp_reduce_scatter"):
+    d = [e["dur"] for e in sorted(ev, key=lambda e: e["ts"]) if pat in e["name"]]
+    n = len(d) // a.steps
+    print(f"\n`{pat}` launch durations of the last step (us): " + " ".join(f"{x:.0f}" for x in d[-n:]))
+
+# timeline window in the forward phase: AdamW launches 10..12 of the last step and every kernel that overlaps them
+ad = [e for e in sorted(ev, key=lambda e: e["ts"]) if "dp_adamw_allgather" in e["name"]]
+n = len(ad) // a.steps
+w0, w1 = ad[-n + 10]["ts"], ad[-n + 12]["ts"] + ad[-n + 12]["dur"]
+print(f"\nTimeline of all streams while AdamW launches 10-12 of the last step run (us from the window start; C = compute stream):\n")
+print("| stream | start | end | kernel |\n|---|---:|---:|---|")
+for e in sorted(ev, key=lambda e: e["ts"]):
+    if e["ts"] + e["dur"] > w0 and e["ts"] < w1:
+        print(f"| {'C' if e['args'].get('stream') == main else 'comm'} | {e['ts'] - w0:.0f} | {e['ts'] + e['dur'] - w0:.0f} | `{e['name'][:50]}` |")
