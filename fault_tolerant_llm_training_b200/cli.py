@@ -97,7 +97,6 @@ def build_parser() -> argparse.ArgumentParser:
     _flag(p, "--save-final", action="store_true",
           help="Also write a checkpoint when training completes (the reference writes none)")
     _flag(p, "--bucket-mb", type=int, default=512, help="Gradient bucket size for dp/fsdp overlap")
-    _flag(p, "--cuda-graph", action="store_true", help="Capture the training step in a CUDA graph")
     return p
 
 

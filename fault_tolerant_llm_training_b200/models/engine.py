@@ -410,7 +410,7 @@ class NativeTrainer:
 
     def __init__(self, cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
                  grad_max_norm: float, clip_mode: str = "clip", seed: int = 0, parallel: str = "none",
-                 bucket_mb: int = 512, cuda_graph: bool = False, keep_shards: bool = False,
+                 bucket_mb: int = 512, keep_shards: bool = False,
                  consolidate: bool = True):
         if dtype != torch.bfloat16:
             raise ValueError("the B200 engine is bf16-only (use --device cpu for other dtypes)")

@@ -86,7 +86,7 @@ def train(args) -> None:
                            warmup_steps=args.lr_warmup_steps, grad_max_norm=args.grad_max_norm,
                            clip_mode=args.clip_mode, seed=args.seed, parallel=args.parallel,
                            fused_optimizer=args.fused_optimizer, bucket_mb=args.bucket_mb,
-                           cuda_graph=args.cuda_graph, keep_shards=args.sharded_checkpoint,
+                           keep_shards=args.sharded_checkpoint,
                            consolidate=not args.no_consolidate, compile_model=args.compile)
     if args.compile:
         logger.info("Using `torch.compile`" if env.device.type != "cuda" else

@@ -103,7 +103,7 @@ class TorchTrainer:
 
 def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
                  grad_max_norm: float = 1.0, clip_mode: str = "clip", seed: int = 0, parallel: str = "auto",
-                 fused_optimizer: bool = False, bucket_mb: int = 512, cuda_graph: bool = False,
+                 fused_optimizer: bool = False, bucket_mb: int = 512,
                  force_torch: bool = False, keep_shards: bool = False, consolidate: bool = True,
                  compile_model: bool = False):
     """Factory used by train.py, bench.py and the tests."""
@@ -125,7 +125,7 @@ def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: floa
 
         return NativeTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps,
                              grad_max_norm=grad_max_norm, clip_mode=clip_mode, seed=seed,
-                             parallel=parallel, bucket_mb=bucket_mb, cuda_graph=cuda_graph,
+                             parallel=parallel, bucket_mb=bucket_mb,
                              keep_shards=keep_shards, consolidate=consolidate)
     return TorchTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps, grad_max_norm=grad_max_norm,
                         clip_mode=clip_mode, seed=seed, fused_optimizer=fused_optimizer, compile_model=compile_model)
