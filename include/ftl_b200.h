@@ -69,6 +69,85 @@ int ftl_grad_norm(const void* g, int64_t n, const float* hyper, float* scratch, 
 int ftl_adamw_step(void* p, const void* g, void* m, void* v, int64_t n, const float* hyper, const float* stats,
                    ftl_stream_t stream);
 
+/* ---- tcgen05 GEMMs (csrc/gemm_tc.cu), bf16 in, fp32 accumulate, bf16 out -------------------------------------------
+ * C[M,N] = op(A) op(B)^T (+ op(A2) op(B2)^T when a2 != NULL: the split reduction used for dgate@W1 + dup@W3).
+ * a_mn / b_mn = 1: the operand is stored with its non-reduction dimension contiguous (no transposes for dgrad/wgrad).
+ * max_ctas > 0 caps the persistent grid (lends SMs to a concurrent communication kernel). */
+int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c, int64_t ldc,
+                  int M, int N, int K, const void* a2, int64_t lda2, const void* b2, int64_t ldb2, int K2, int max_ctas,
+                  ftl_stream_t stream);
+/* act = silu(x W1^T) * (x W3^T); gate / up (pre-activations, kept for the backward) may be NULL */
+int ftl_gemm_swiglu(const void* x, int64_t ldx, const void* w1, const void* w3, int64_t ldw, void* act, void* gate,
+                    void* up, int64_t ldo, int M, int H, int K, int max_ctas, ftl_stream_t stream);
+/* qkv = x Wqkv^T with the rotary embedding applied to the first rot_cols output columns in the epilogue */
+int ftl_gemm_qkv_rope(const void* x, int64_t ldx, const void* wqkv, int64_t ldw, void* qkv, int64_t ldo,
+                      const float* cos_t, const float* sin_t, int M, int N, int K, int seq_len, int head_dim,
+                      int rot_cols, int max_ctas, ftl_stream_t stream);
+/* Same two GEMMs with the weight all-gather fused in (fully-sharded mode): the epilogue warps pull 16-row slices of the
+ * peers' shards into wqkv / w1 / w3 while the producer waits per 128-row block.  scratch: int[2 * blocks], zeroed. */
+int ftl_gemm_qkv_rope_gather(const void* x, int64_t ldx, void* wqkv, int64_t ldw, void* qkv, int64_t ldo,
+                             const float* cos_t, const float* sin_t, int M, int N, int K, int seq_len, int head_dim,
+                             int rot_cols, const void* const* peer_shards, int64_t shard_off, int rows_per_rank,
+                             int rank, int world, int* scratch, ftl_stream_t stream);
+int ftl_gemm_swiglu_gather(const void* x, int64_t ldx, void* w1, void* w3, int64_t ldw, void* act, void* gate, void* up,
+                           int64_t ldo, int M, int H, int K, const void* const* peer_shards, int64_t shard_off_w1,
+                           int64_t shard_off_w3, int rows_per_rank, int rank, int world, int* scratch,
+                           ftl_stream_t stream);
+
+/* ---- tcgen05 flash attention (csrc/attn_tc.cu): causal, grouped-query, reads q|k|v in place from the fused projection
+ * qkv: [B*S, ld_qkv] = q heads | k heads | v heads (RoPE already applied); out: [B*S, ld_out]; lse: fp32 [B, H, S]
+ * (log2 domain).  S % 128 == 0, hd in {64, 128}.  The backward writes dq | dk | dv into dqkv ([B*S, ld_qkv]) and, when
+ * cos_t / sin_t are given, applies the inverse rotary embedding to dq and dk.  delta: fp32 [B, H, S] work area;
+ * scratch: ftl_attn_bwd_scratch_bytes() bytes.  Forward and backward are bitwise reproducible.  Work items are handed
+ * out through per-device queue words inside the library: keep the launches of one GPU on one stream. */
+int ftl_attn_fwd(const void* qkv, int64_t ld_qkv, void* out, int64_t ld_out, float* lse, int B, int S, int H, int KV,
+                 int hd, ftl_stream_t stream);
+int64_t ftl_attn_bwd_scratch_bytes(int B, int S, int H, int KV, int hd);
+int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const void* d_out, int64_t ld_out, const float* lse,
+                 float* delta, void* dqkv, const float* cos_t, const float* sin_t, float* scratch, int B, int S, int H,
+                 int KV, int hd, ftl_stream_t stream);
+
+/* ---- NVLink data plane (csrc/comm.cu): symmetric buffers over CUDA IPC, device barriers, fused collectives -----------
+ * peer_* arguments are device arrays of `world` pointers (this rank's own buffer at index `rank`).
+ * status: device uint32, 0 ok / 1 barrier timed out / 2 a peer raised the abort word; sticky, every kernel below becomes
+ * a no-op once it is non-zero.  commits: device uint64 counting applied updates (may be NULL). */
+int ftl_symm_alloc(void** ptr, int64_t bytes);                  /* set-up time only: allocates */
+int ftl_symm_free(void* ptr);
+int ftl_ipc_export(void* ptr, void* handle64);                  /* 64-byte handle to send to the peers */
+int ftl_ipc_import(const void* handle64, void** ptr);
+int ftl_ipc_close(void* ptr);
+int ftl_comm_max_ranks(void);
+int ftl_comm_flag_words(void);                                  /* uint32 words of a rank's flag area */
+int ftl_barrier(void* const* peer_flags, int rank, int world, uint32_t epoch, void* status, int64_t timeout_ms,
+                ftl_stream_t stream);
+int ftl_raise_abort(void* const* peer_flags, int world, ftl_stream_t stream);
+int ftl_dp_partials(int max_ctas);                              /* floats of `partial` one reduce-scatter launch writes */
+/* gradient range [lo, lo+n) of every rank summed in rank order into this rank's buffer, with the sum of squares of the
+ * result in `partial` (reduce-scatter fused with the norm) */
+int ftl_dp_reduce_scatter(void* const* peer_g, int rank, int world, int64_t lo, int64_t n, float* partial,
+                          const void* status, int max_ctas, ftl_stream_t stream);
+int ftl_dp_publish(const float* partial, int nparts, const float* loss_local, void* const* peer_slots, int rank,
+                   int world, ftl_stream_t stream);
+int ftl_dp_finalize(const float* slots, int world, const float* hyper, float* stats, float* loss_out, int clip,
+                    ftl_stream_t stream);
+/* clip + AdamW on parameter range [lo, lo+n) with every updated vector stored to all ranks' copies (all-gather fused) */
+int ftl_dp_adamw_allgather(void* const* peer_p, const void* g, void* m, void* v, int rank, int world, int64_t lo,
+                           int64_t n, const float* hyper, const float* stats, const void* status, void* commits,
+                           int max_ctas, ftl_stream_t stream);
+int ftl_fsdp_gather(const void* const* peer_shards, int64_t off, void* dst, int64_t n_per_rank, int rank, int world,
+                    const void* status, int max_ctas, ftl_stream_t stream);
+int ftl_adamw_shard(void* p, const void* g, void* m, void* v, int64_t n, const float* hyper, const float* stats,
+                    const void* status, void* commits, int max_ctas, ftl_stream_t stream);
+
+/* ---- checkpoint snapshot engine (csrc/ckpt_io.cu): device segments <-> one file through pinned double buffers ---------
+ * timings (double[4], may be NULL) = d2h (h2d), write (read), fsync, total seconds.  Returns 0 or -1 (ftl_ckpt_last_error). */
+int ftl_ckpt_init(int64_t stage_bytes);
+int ftl_ckpt_write(const char* path, int nseg, const void* const* dev_ptrs, const int64_t* sizes,
+                   const int64_t* file_offsets, int nthreads, int do_fsync, double* timings);
+int ftl_ckpt_read(const char* path, int nseg, void* const* dev_ptrs, const int64_t* sizes, const int64_t* file_offsets,
+                  int nthreads, double* timings);
+const char* ftl_ckpt_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -157,6 +157,34 @@ def test_grad_norm_and_adamw_match_torch(N):
     assert float(stats[2]) == 0.0 and torch.equal(p, before)
 
 
+def test_attention_tc_model_shape_vs_sdpa(N):
+    """Model shape (32 query / 8 kv heads, head_dim 128, S = 2048): more work items than SMs, so the dynamic work queues,
+    the two-tile forward with lazy rescale and the chunked dK/dV units with their reduction all run.  Oracle: the library
+    SDPA on the same bf16 inputs (the fp32 einsum oracle of the small cases would need 2 GB of scores)."""
+    import torch.nn.functional as F
+    B, S, H, KV, hd = 1, 2048, 32, 8, 128
+    W = (H + 2 * KV) * hd
+    qkv, dout = bf(B * S, W, scale=0.7, seed=11), bf(B * S, H * hd, scale=0.5, seed=12)
+    out = torch.empty(B * S, H * hd, device=DEV, dtype=torch.bfloat16)
+    lse, delta = torch.empty(B * H * S, device=DEV), torch.empty(B * H * S, device=DEV)
+    dqkv = torch.zeros_like(qkv)
+    N.attn_fwd(qkv, out, lse, B, S, H, KV, hd)
+    N.attn_bwd(qkv, out, dout, lse, delta, dqkv, B, S, H, KV, hd)
+    x = qkv.view(B, S, H + 2 * KV, hd)
+    q, k, v = (t.transpose(1, 2).clone().requires_grad_() for t in (x[:, :, :H], x[:, :, H:H + KV], x[:, :, H + KV:]))
+    ref = F.scaled_dot_product_attention(q, k.repeat_interleave(H // KV, 1), v.repeat_interleave(H // KV, 1), is_causal=True)
+    ref.backward(dout.view(B, S, H, hd).transpose(1, 2))
+    d4 = dqkv.view(B, S, -1, hd)
+    assert _rel(out.view(B, S, H, hd), ref.detach().transpose(1, 2).float()) < 1e-2
+    for got, want in ((d4[:, :, :H], q.grad), (d4[:, :, H:H + KV], k.grad), (d4[:, :, H + KV:], v.grad)):
+        assert _rel(got, want.transpose(1, 2).float()) < 2e-2
+    out2, dq2 = torch.empty_like(out), torch.zeros_like(dqkv)
+    for _ in range(2):                                   # the queues reset themselves: a second and third launch agree bitwise
+        N.attn_fwd(qkv, out2, lse, B, S, H, KV, hd)
+        N.attn_bwd(qkv, out2, dout, lse, delta, dq2, B, S, H, KV, hd)
+        assert torch.equal(out, out2) and torch.equal(dqkv, dq2)
+
+
 def test_adamw_untouched_rows_exact(N):
     """Elements with g = m = v = 0 (embedding rows no batch has touched) only see the weight decay: the clamp that keeps
     sqrtf() off its zero/subnormal slow path (adam_vmin, csrc/common/util.cuh) must not change a bit of the result."""

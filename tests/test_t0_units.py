@@ -136,3 +136,17 @@ def test_handle_exit_failed_resubmit(tmp_path, monkeypatch, caplog):
         handle_exit(None, None, None, 1, str(tmp_path), 10, logging.getLogger("t0"), save_fn=rec.save,
                     resubmit_cmd="false")
     assert "[EXIT HANDLER] Failed to requeue job 9." in caplog.text
+
+
+def test_c_header_declares_every_entry_point():
+    """include/ftl_b200.h is the documented C ABI: every exported function of csrc/ must be declared."""
+    import glob
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "ftl_b200.h")).read()
+    declared = set(re.findall(r"\b(ftl_[a-z0-9_]+)\s*\(", header))
+    defined = set()
+    for path in glob.glob(os.path.join(root, "csrc", "*.cu")):
+        defined |= set(re.findall(r"^FTL_API\s+[\w\s\*]+?\b(ftl_[a-z0-9_]+)\s*\(", open(path).read(), flags=re.M))
+    defined.discard("ftl_attn_dbg_read")            # probe build only (FTL_ATTN_DEBUG)
+    assert len(defined) > 40 and not (defined - declared), sorted(defined - declared)
