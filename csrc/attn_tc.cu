@@ -9,18 +9,25 @@
 // the library backward that this replaces accumulates dQ with atomics at sequence lengths >= 4096
 // (tools/determinism_check.py), which breaks the bitwise kill/resume guarantee.
 //
-//   attn_fwd_kernel   CTA = (batch, q head, 128-query tile); per 128-key tile: S = Q K^T (TMEM) -> online softmax in
-//                     registers (thread = query row) -> P (bf16) to swizzled smem -> O_tile = P V (TMEM) -> rescale
-//                     and add in registers.  Writes O (bf16) and the row log-sum-exp (fp32, base 2 domain).
-//   attn_bwd_dkv      CTA = (batch, kv head, 128-key tile); loops over the group's query heads and 64-query tiles:
-//                     S^T = K Q^T, dP^T = V dO^T (TMEM) -> P^T, dS^T (thread = key row) to smem ->
-//                     dV += P^T dO, dK += dS^T Q accumulated in TMEM over the whole loop.
-//   attn_bwd_dq       CTA = (batch, q head, 128-query tile); loops over 64-key tiles: S = Q K^T, dP = dO V^T ->
-//                     dS (thread = query row) to smem -> dQ += dS K accumulated in TMEM.
-//   attn_delta        delta[t, h] = sum_d dO * O   (fp32), the softmax-backward row term.
-// Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2-9 = 256 math threads: TMEM lane quarter
-// warp % 4 (a hardware rule), column half (warp - 2) / 4, so every tile row is served by two threads on different
-// schedulers and TMEM / MUFU latency of one hides behind the other.
+//   attn_fwd2_kernel  (S % 256 == 0) CTA = (batch, q head, TWO 128-query tiles); two softmax warpgroups (thread = whole
+//                     query row) ping-pong under the MMAs of the other tile, O accumulates in TMEM with a lazy rescale
+//                     done by a correction warpgroup, P is a TMEM A operand; dynamic causal work queue.
+//   attn_fwd_kernel   (other S) CTA = (batch, q head, 128-query tile); per 128-key tile: S = Q K^T (TMEM) -> online
+//                     softmax in registers (two threads per query row) -> P (bf16, TMEM) -> O_tile = P V (TMEM) ->
+//                     rescale and add in registers.  Both write O (bf16) and the row log-sum-exp (fp32, base 2).
+//   attn_bwd_dq       CTA = (batch, q head, 128-query tile); Q and dO are written once per item into TMEM as bf16 A
+//                     operands; loops over 64-key tiles: S = Q K^T, dP = dO V^T -> dS (thread = query row, written over
+//                     its own dP columns) -> dQ += dS K.  All three MMAs take A from TMEM; shared memory carries only
+//                     the K/V ring.  While staging it also computes delta[t, h] = sum_d dO * O (the softmax-backward
+//                     row term) and leaves it in global memory for attn_bwd_dkv, which runs after it.
+//   attn_bwd_dkv      CTA = (batch, kv head, 128-key tile) or a chunk of its loop over the group's query heads and
+//                     64-query tiles: S^T = K Q^T, dP^T = V dO^T (TMEM) -> P^T, dS^T (thread = key row, written over
+//                     its own score columns) -> dV += P^T dO, dK += dS^T Q with A from TMEM.  Chunks leave fp32
+//                     partials that attn_dkv_reduce folds in chunk order.
+// Work items of all three kernels come from atomic queues, longest first (causal items differ 10x in length).
+// Warp roles of the backward kernels and attn_fwd_kernel: warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2-9 = 256 math threads: TMEM lane quarter warp % 4 (a hardware rule), column half (warp - 2) / 4.
+// How these shapes were chosen and what limits them: profiles/attn_tc_notes.md, profiles/umma_shapes.md.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cudaTypedefs.h>
@@ -91,6 +98,8 @@ struct AttnArgs {
     float* partial;                // [units][2][128][hd] fp32
     const __nv_bfloat16* qkv_in;   // backward: the forward's fused projection and dO, read directly by the dQ kernel
     const __nv_bfloat16* dout_in;
+    const __nv_bfloat16* o_in;     // forward output (delta = rowsum(dO * O) is computed by the dQ kernel)
+    float* delta_out;
     int64_t ld_do;
 };
 
@@ -717,27 +726,6 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
     if (warp == 12) ptx::tmem_dealloc<512>(tmem);
 }
 
-// ================================================================================================= delta
-// delta[b, h, s] = sum_d dO[t, h, d] * O[t, h, d]; one warp per (token, head).
-__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
-                                  float* __restrict__ delta, int B, int S, int H, int HD, int64_t ld) {
-    const int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (w >= (int64_t)B * S * H) return;
-    const int64_t t = w / H;
-    const int h = (int)(w % H);
-    float s = 0.f;
-    for (int i = lane * 8; i < HD; i += 256) {
-        float x[8], y[8];
-        unpack8(ld8(o + t * ld + h * HD + i), x);
-        unpack8(ld8(d_o + t * ld + h * HD + i), y);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s += x[k] * y[k];
-    }
-    s = warp_sum(s);
-    if (lane == 0) delta[((int64_t)(t / S) * H + h) * S + (t % S)] = s;
-}
-
 // inverse rotary embedding of 8 consecutive gradient values (4 pairs) of a q / k row at position pos
 __device__ __forceinline__ void unrope8(float (&f)[8], const AttnArgs& a, int pos, int d0, int hd) {
     if (!a.cos_t) return;
@@ -1121,6 +1109,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
     uint64_t* item_empty = bars + 26;// 2: MMA warp + 8 math warps have read it
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 28);
     int* sItem = reinterpret_cast<int*>(bars + 29);    // [2]
+    float* sDelta = reinterpret_cast<float*>(bars + 32);   // [2][2][BM] halves of the row dot products dO . O
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q_tiles = a.S / BM, rep = a.H / a.KV;
@@ -1236,19 +1225,35 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
         const uint32_t lane_addr = (uint32_t)(q4 * 32) << 16;
         const int c0 = half * 32;
         const uint64_t scale2 = ptx::pack_f32x2(a.scale_log2, a.scale_log2);
-        // this thread's half of the Q and dO rows of an item: global -> registers -> TMEM (bf16 pairs, HD/4 columns each)
-        auto stage_rows = [&](int it2) {
+        // This thread's half of the Q and dO rows of an item: global -> registers (load_rows, issued BEFORE the wait for
+        // the previous item's last MMAs so that the load latency hides behind it) -> TMEM as bf16 pairs, HD/4 columns each
+        // (publish_rows, once the previous item no longer reads these columns).
+        uint32_t vq[HD / 4], vd[HD / 4];
+        float dot_half = 0.f, delta_staged = 0.f;                      // half of / whole delta of row r of the staged item
+        int64_t delta_idx = 0;
+        int stage_n = 0;
+        auto load_rows = [&](int it2) {
             int b2, h2, qt2; decode(it2, b2, h2, qt2);
             const int64_t tok = (int64_t)b2 * a.S + qt2 * BM + r;
             const uint4* qrow = reinterpret_cast<const uint4*>(a.qkv_in + tok * a.ld_qkv + h2 * HD + half * (HD / 2));
             const uint4* drow = reinterpret_cast<const uint4*>(a.dout_in + tok * a.ld_do + h2 * HD + half * (HD / 2));
-            uint32_t vq[HD / 4], vd[HD / 4];
+            const uint4* orow = reinterpret_cast<const uint4*>(a.o_in + tok * a.ld_do + h2 * HD + half * (HD / 2));
+            delta_idx = ((int64_t)b2 * a.H + h2) * a.S + qt2 * BM + r;
+            float dot = 0.f;                                           // this half of delta = sum_d dO * O of the row
 #pragma unroll
             for (int i = 0; i < HD / 16; ++i) {
-                const uint4 x = qrow[i], y = drow[i];
+                const uint4 x = qrow[i], y = drow[i], z = orow[i];
                 vq[4 * i] = x.x; vq[4 * i + 1] = x.y; vq[4 * i + 2] = x.z; vq[4 * i + 3] = x.w;
                 vd[4 * i] = y.x; vd[4 * i + 1] = y.y; vd[4 * i + 2] = y.z; vd[4 * i + 3] = y.w;
+                float fo[8], fd[8];
+                unpack8(*reinterpret_cast<const bf16x8*>(&z), fo);
+                unpack8(*reinterpret_cast<const bf16x8*>(&y), fd);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) dot = fmaf(fo[k], fd[k], dot);
             }
+            dot_half = dot;
+        };
+        auto publish_rows = [&]() {
             if constexpr (HD == 128) {
                 ptx::tmem_st32(tmem + kTmQ + lane_addr + half * (HD / 4), vq);
                 ptx::tmem_st32(tmem + kTmDO + lane_addr + half * (HD / 4), vd);
@@ -1260,6 +1265,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(qd_full);
+            // the two threads of a row add their halves in a fixed order; the row's delta also goes to global memory for
+            // the dK/dV kernel, which runs after this one (this replaced a separate kernel that re-read O and dO)
+            float* xd = sDelta + (stage_n & 1) * 2 * BM;
+            xd[half * BM + r] = dot_half;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            delta_staged = xd[r] + xd[BM + r];
+            if (half == 0) a.delta_out[delta_idx] = delta_staged;
+            ++stage_n;
         };
         int item_it = 0, n_it = 0;
         auto next_item = [&](int idx) {                                // idx-th item of this CTA (-1: queue drained)
@@ -1271,12 +1284,12 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
             return v;
         };
         int it = next_item(0);
-        if (it >= 0) stage_rows(it);
+        if (it >= 0) { load_rows(it); publish_rows(); }
         for (; it >= 0; ++item_it) {
             int b, h, qt; decode(it, b, h, qt);
             const int qi = qt * BM + r;
             const int64_t so = ((int64_t)b * a.H + h) * a.S + qi;
-            const float lse = a.lse[so], delta = a.delta[so];
+            const float lse = a.lse[so], delta = delta_staged;         // staged before the next item's staging overwrites it
             const uint64_t nlse2 = ptx::pack_f32x2(-lse, -lse), ndel2 = ptx::pack_f32x2(-delta, -delta);
             const int nkv = (qt + 1) * (BM / BN);
             for (int j = 0; j < nkv; ++j, ++n_it) {
@@ -1314,10 +1327,11 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&t_full[st]);
             }
+            const int it_next = next_item(item_it + 1);
+            if (it_next >= 0) load_rows(it_next);                        // in flight while the last MMAs of this item drain
             ptx::mbar_wait(acc_full, item_it & 1);                       // every MMA of the item has completed
             ptx::tc_fence_after();
-            const int it_next = next_item(item_it + 1);
-            if (it_next >= 0) stage_rows(it_next);                       // next Q, dO: S, dP of its first tile start under the epilogue
+            if (it_next >= 0) publish_rows();                            // next Q, dO: S, dP of its first tile start under the epilogue
             __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD;
 #pragma unroll 1
             for (int c = half * (HD / 2); c < (half + 1) * (HD / 2); c += 32) {
@@ -1462,12 +1476,6 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
     if ((e = attn_tmap(&tq64, qkv, T, (int64_t)(H + 2 * KV) * hd, ld_qkv, 64))) return e;
     if ((e = attn_tmap(&tdo128, d_out, T, (int64_t)H * hd, ld_out, 128))) return e;
     if ((e = attn_tmap(&tdo64, d_out, T, (int64_t)H * hd, ld_out, 64))) return e;
-    {
-        const int64_t warps = T * H;
-        attn_delta_kernel<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, stream>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)d_out,
-                                                                                   delta, B, S, H, hd, ld_out);
-        FTL_LAUNCH_CHECK();
-    }
     AttnArgs a{};
     a.cos_t = cos_t; a.sin_t = sin_t;
     a.out = (__nv_bfloat16*)dqkv; a.ld_out = ld_qkv; a.lse = const_cast<float*>(lse); a.delta = delta;
@@ -1476,35 +1484,38 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
     dkv_plan(B, S, H, KV, &a.chunk_len, &a.units);
     a.partial = scratch;
     a.qkv_in = (const __nv_bfloat16*)qkv; a.dout_in = (const __nv_bfloat16*)d_out; a.ld_do = ld_out;
+    a.o_in = (const __nv_bfloat16*)out; a.delta_out = delta;
     const int items_kv = a.units, items_q = B * H * (S / 128), items_red = B * KV * (S / 128);
     if (hd == 128) {
         constexpr int smem_kv = 2 * 128 * 128 * 2 + 8 * 64 * 128 * 2 + 4 * 64 * 4 + 1024 + 256;   // K, V, 4 x (Q, dO)
-        constexpr int smem_q = 12 * 64 * 128 * 2 + 1024 + 256;                     // K / V ring only
+        constexpr int smem_q = 12 * 64 * 128 * 2 + 256 + 2048 + 256;               // K / V ring, barriers, delta exchange
         static bool once = false;
         if (!once) {
             if ((e = set_smem(attn_bwd_dkv_kernel<128>, smem_kv))) return e;
             if ((e = set_smem(attn_bwd_dq_kernel<128>, smem_q))) return e;
             once = true;
         }
+        // dQ first: it also produces delta = rowsum(dO * O), which the dK/dV kernel reads
+        attn_bwd_dq_kernel<128><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq64, a);
+        FTL_LAUNCH_CHECK();
         attn_bwd_dkv_kernel<128><<<items_kv < kNumSMs ? items_kv : kNumSMs, kAttnThreads, smem_kv, stream>>>(tq128, tq64, tdo64, a);
         FTL_LAUNCH_CHECK();
         attn_dkv_reduce_kernel<128><<<items_red * 16, 128, 0, stream>>>(a);
-        FTL_LAUNCH_CHECK();
-        attn_bwd_dq_kernel<128><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq64, a);
     } else {
         constexpr int smem_kv = 2 * 128 * 64 * 2 + 8 * 64 * 64 * 2 + 4 * 64 * 4 + 1024 + 256;
-        constexpr int smem_q = 12 * 64 * 64 * 2 + 1024 + 256;
+        constexpr int smem_q = 12 * 64 * 64 * 2 + 256 + 2048 + 256;
         static bool once = false;
         if (!once) {
             if ((e = set_smem(attn_bwd_dkv_kernel<64>, smem_kv))) return e;
             if ((e = set_smem(attn_bwd_dq_kernel<64>, smem_q))) return e;
             once = true;
         }
+        // dQ first: it also produces delta = rowsum(dO * O), which the dK/dV kernel reads
+        attn_bwd_dq_kernel<64><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq64, a);
+        FTL_LAUNCH_CHECK();
         attn_bwd_dkv_kernel<64><<<items_kv < kNumSMs ? items_kv : kNumSMs, kAttnThreads, smem_kv, stream>>>(tq128, tq64, tdo64, a);
         FTL_LAUNCH_CHECK();
         attn_dkv_reduce_kernel<64><<<items_red * 16, 64, 0, stream>>>(a);
-        FTL_LAUNCH_CHECK();
-        attn_bwd_dq_kernel<64><<<items_q < kNumSMs ? items_q : kNumSMs, kAttnThreads, smem_q, stream>>>(tq64, a);
     }
     return (int)cudaGetLastError();
 }
