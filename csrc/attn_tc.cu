@@ -135,11 +135,22 @@ __device__ __forceinline__ void umma_tile_ts(uint32_t tmem_d, uint32_t tmem_a, u
 // Timestamp probe (tools/attn_probe.py builds a separate library with this defined): CTA 0 records clock64 at fixed
 // points of its first item, per key tile.  Slots 0-7 math thread (warp 2 lane 0), 8-15 MMA thread.
 __device__ long long g_attn_dbg[64 * 16];
+#ifdef FTL_PROBE_DQ
+#define ATTN_DBG(cond, tile, slot) do { } while (0)
+#else
 #define ATTN_DBG(cond, tile, slot) do { if (blockIdx.x == 0 && (cond) && (tile) < 64) g_attn_dbg[(tile) * 16 + (slot)] = clock64(); } while (0)
+#endif
+#ifdef FTL_PROBE_DQ     // the dQ and dK/dV kernels run in one call and share the array: probe one of them per build
+#define DQ_DBG(cond, tile, slot) do { if (blockIdx.x == 0 && (cond) && (tile) < 64) g_attn_dbg[(tile) * 16 + (slot)] = clock64(); } while (0)
+#define KV_DBG(cond, tile, slot) do { } while (0)
+#else
 #define KV_DBG(cond, tile, slot) do { if (blockIdx.x == 0 && (cond) && (tile) < 64) g_attn_dbg[(tile) * 16 + (slot)] = clock64(); } while (0)
+#define DQ_DBG(cond, tile, slot) do { } while (0)
+#endif
 #else
 #define ATTN_DBG(cond, tile, slot) do { } while (0)
 #define KV_DBG(cond, tile, slot) do { } while (0)
+#define DQ_DBG(cond, tile, slot) do { } while (0)
 #endif
 
 // ================================================================================================= forward
@@ -363,11 +374,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
             const float inv = 1.f / l;
             __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD + d0;
 #pragma unroll
-            for (int d = 0; d < OW; d += 8) {
-                float o[8];
+            for (int d = 0; d < OW; d += 16) {
+                float o[8], o2[8];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) o[i] = acc[d + i] * inv;
-                st8(orow + d, pack8(o));
+                for (int i = 0; i < 8; ++i) { o[i] = acc[d + i] * inv; o2[i] = acc[d + 8 + i] * inv; }
+                st_row32(orow + d, pack8(o), pack8(o2));                 // full 32-byte sectors (see util.cuh)
             }
             if (half == 0) a.lse[((int64_t)b * a.H + h) * a.S + qi] = m + log2f(l);
             asm volatile("bar.sync 1, 256;" ::: "memory");              // exchange buffer free again for the next item
@@ -711,11 +722,11 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
                     ptx::tmem_ld32(to + d, v);
                     ptx::tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; i += 8) {
-                        float o[8];
+                    for (int i = 0; i < 32; i += 16) {
+                        float o[8], o2[8];
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) o[k] = __uint_as_float(v[i + k]) * inv;
-                        st8(orow + d + i, pack8(o));
+                        for (int k = 0; k < 8; ++k) { o[k] = __uint_as_float(v[i + k]) * inv; o2[k] = __uint_as_float(v[i + 8 + k]) * inv; }
+                        st_row32(orow + d + i, pack8(o), pack8(o2));     // full 32-byte sectors (see util.cuh)
                     }
                 }
             }
@@ -1015,25 +1026,23 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                     float* pv = a.partial + (((int64_t)it * 2 + 0) * BK + r) * HD + c;
                     float* pk = a.partial + (((int64_t)it * 2 + 1) * BK + r) * HD + c;
 #pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        *reinterpret_cast<float4*>(pv + i) = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]),
-                                                                         __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
-                        *reinterpret_cast<float4*>(pk + i) = make_float4(__uint_as_float(kk[i]), __uint_as_float(kk[i + 1]),
-                                                                         __uint_as_float(kk[i + 2]), __uint_as_float(kk[i + 3]));
-                    }
+                    for (int i = 0; i < 32; i += 8) { st8f(pv + i, v + i); st8f(pk + i, kk + i); }   // 32-byte stores
                     continue;
                 }
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    float fv[8], fk[8];
+                for (int u = 0; u < 4; u += 2) {
+                    float fv[8], fk[8], fv2[8], fk2[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         fv[i] = __uint_as_float(v[u * 8 + i]);
                         fk[i] = __uint_as_float(kk[u * 8 + i]) * a.scale;
+                        fv2[i] = __uint_as_float(v[u * 8 + 8 + i]);
+                        fk2[i] = __uint_as_float(kk[u * 8 + 8 + i]) * a.scale;
                     }
                     unrope8(fk, a, kj, c + u * 8, HD);
-                    st8(a.out + trow + (a.H + a.KV + g) * HD + c + u * 8, pack8(fv));
-                    st8(a.out + trow + (a.H + g) * HD + c + u * 8, pack8(fk));
+                    unrope8(fk2, a, kj, c + u * 8 + 8, HD);
+                    st_row32(a.out + trow + (a.H + a.KV + g) * HD + c + u * 8, pack8(fv), pack8(fv2));
+                    st_row32(a.out + trow + (a.H + g) * HD + c + u * 8, pack8(fk), pack8(fk2));
                 }
             }
             ptx::tc_fence_before();
@@ -1287,6 +1296,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
         if (it >= 0) { load_rows(it); publish_rows(); }
         for (; it >= 0; ++item_it) {
             int b, h, qt; decode(it, b, h, qt);
+            DQ_DBG(threadIdx.x == 64, item_it, 0);
             const int qi = qt * BM + r;
             const int64_t so = ((int64_t)b * a.H + h) * a.S + qi;
             const float lse = a.lse[so], delta = delta_staged;         // staged before the next item's staging overwrites it
@@ -1296,6 +1306,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
                 const int st = n_it & 1;
                 ptx::mbar_wait(&s_full[st], (n_it >> 1) & 1);
                 ptx::tc_fence_after();
+                if (j == 0) DQ_DBG(threadIdx.x == 64, item_it, 1);
                 const bool diag = j * BN + BN > qt * BM;
                 // dS = exp2(S * scale - lse) * (dP - delta) on packed fp32 pairs (see attn_bwd_dkv_kernel)
                 auto block = [&](auto diag_c) {
@@ -1327,29 +1338,43 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(&t_full[st]);
             }
+            DQ_DBG(threadIdx.x == 64, item_it, 2);
             const int it_next = next_item(item_it + 1);
             if (it_next >= 0) load_rows(it_next);                        // in flight while the last MMAs of this item drain
+            DQ_DBG(threadIdx.x == 64, item_it, 3);
             ptx::mbar_wait(acc_full, item_it & 1);                       // every MMA of the item has completed
             ptx::tc_fence_after();
-            if (it_next >= 0) publish_rows();                            // next Q, dO: S, dP of its first tile start under the epilogue
+            DQ_DBG(threadIdx.x == 64, item_it, 4);
+            if (it_next >= 0) publish_rows();
+            DQ_DBG(threadIdx.x == 64, item_it, 5);                            // next Q, dO: S, dP of its first tile start under the epilogue
             __nv_bfloat16* orow = a.out + (int64_t)(b * a.S + qi) * a.ld_out + h * HD;
 #pragma unroll 1
             for (int c = half * (HD / 2); c < (half + 1) * (HD / 2); c += 32) {
                 uint32_t v[32];
                 ptx::tmem_ld32(tmem + kTmDQ + lane_addr + c, v);
                 ptx::tmem_ld_wait();
+                DQ_DBG(threadIdx.x == 64, item_it, c == 0 ? 8 : 10);
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    float f[8];
+                for (int u = 0; u < 4; u += 2) {
+                    float f[8], f2[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(v[u * 8 + i]) * a.scale;
+                    for (int i = 0; i < 8; ++i) {
+                        f[i] = __uint_as_float(v[u * 8 + i]) * a.scale;
+                        f2[i] = __uint_as_float(v[u * 8 + 8 + i]) * a.scale;
+                    }
                     unrope8(f, a, qi, c + u * 8, HD);
-                    st8(orow + c + u * 8, pack8(f));
+                    unrope8(f2, a, qi, c + u * 8 + 8, HD);
+                    st_row32(orow + c + u * 8, pack8(f), pack8(f2));        // full 32-byte sectors
                 }
+                DQ_DBG(threadIdx.x == 64, item_it, c == 0 ? 9 : 11);
             }
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(acc_empty);
+            DQ_DBG(threadIdx.x == 64, item_it, 6);
+#if defined(FTL_ATTN_DEBUG) && defined(FTL_PROBE_DQ)
+            if (blockIdx.x == 0 && threadIdx.x == 64 && item_it < 64) g_attn_dbg[item_it * 16 + 7] = nkv;
+#endif
             it = it_next;
         }
     }
@@ -1399,7 +1424,9 @@ FTL_API int ftl_attn_dbg_read(long long* host) {
 
 FTL_API int ftl_attn_fwd(const void* qkv, int64_t ld_qkv, void* out, int64_t ld_out, float* lse, int B, int S, int H, int KV,
                          int hd, cudaStream_t stream) {
-    if (S % 128 || (hd != 64 && hd != 128) || H % KV || ld_qkv % 8 || ld_out % 8) return (int)cudaErrorInvalidValue;
+    // rows are written with 32-byte stores: strides in multiples of 16 elements, 32-byte aligned bases
+    if (S % 128 || (hd != 64 && hd != 128) || H % KV || ld_qkv % 16 || ld_out % 16 || ((uintptr_t)out & 31))
+        return (int)cudaErrorInvalidValue;
     CUtensorMap tm;
     int e = attn_tmap(&tm, qkv, (int64_t)B * S, (int64_t)(H + 2 * KV) * hd, ld_qkv, 128);
     if (e) return e;
@@ -1468,7 +1495,9 @@ FTL_API int64_t ftl_attn_bwd_scratch_bytes(int B, int S, int H, int KV, int hd) 
 FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const void* d_out, int64_t ld_out, const float* lse,
                          float* delta, void* dqkv, const float* cos_t, const float* sin_t, float* scratch, int B, int S, int H,
                          int KV, int hd, cudaStream_t stream) {
-    if (S % 128 || (hd != 64 && hd != 128) || H % KV || ld_qkv % 8 || ld_out % 8) return (int)cudaErrorInvalidValue;
+    if (S % 128 || (hd != 64 && hd != 128) || H % KV || ld_qkv % 16 || ld_out % 16 || ((uintptr_t)dqkv & 31) ||
+        ((uintptr_t)scratch & 31))
+        return (int)cudaErrorInvalidValue;
     const int64_t T = (int64_t)B * S;
     CUtensorMap tq128, tq64, tdo128, tdo64;
     int e;

@@ -26,6 +26,19 @@ __device__ __forceinline__ bf16x8 ld8(const __nv_bfloat16* p) {
 __device__ __forceinline__ void st8(__nv_bfloat16* p, const bf16x8& x) {
     *reinterpret_cast<bf16x8*>(p) = x;
 }
+// 32-byte stores (sm_100: 256-bit global accesses): a thread that owns a whole row segment writes full 32-byte sectors,
+// where two 16-byte stores from different instructions each reach L2 as a partial-sector write (read-modify-write when
+// the line is not resident).  The attention epilogues, one row per thread, spent ~9 us per 32 KB tile on those.
+__device__ __forceinline__ void st_row32(__nv_bfloat16* p, const bf16x8& x, const bf16x8& y) {
+    const int4& a = *reinterpret_cast<const int4*>(&x);
+    const int4& b = *reinterpret_cast<const int4*>(&y);
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w) : "memory");
+}
+__device__ __forceinline__ void st8f(float* p, const uint32_t* v) {      // 8 fp32 values given as raw bits
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+}
 // streaming variants: data touched once (optimizer state, gradients) should not displace L2 residents
 __device__ __forceinline__ bf16x8 ld8_stream(const __nv_bfloat16* p) {
     int4 r;

@@ -124,11 +124,32 @@ __device__ __forceinline__ void st16(__nv_bfloat16* p, const bf16x8& v) {
     asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w) : "memory");
 }
 
+// Two adjacent 8-column groups of a row go out as ONE 32-byte store when the layout allows it (row stride and base
+// 32-byte aligned, both groups inside N): a thread owns its row, so 16-byte stores issued by different instructions
+// reach L2 as partial-sector writes (read-modify-write when the line is not resident) - the same pathology that cost
+// the attention epilogues 9 us per 32 KB tile.
+__device__ __forceinline__ void store_groups(__nv_bfloat16* base, bool wide, int64_t off, const bf16x8 (&o)[4], int col0, int n_cols) {
+#pragma unroll
+    for (int v = 0; v < 4; v += 2) {
+        const int col = col0 + v * 8;
+        if (wide && col + 16 <= n_cols) {
+            st_row32(base + off + v * 8, o[v], o[v + 1]);
+        } else {
+            if (col < n_cols) st16(base + off + v * 8, o[v]);
+            if (col + 8 < n_cols) st16(base + off + v * 8 + 8, o[v + 1]);
+        }
+    }
+}
+__device__ __forceinline__ bool wide_ok(const void* p, int64_t ld) {
+    return p != nullptr && (ld & 15) == 0 && (reinterpret_cast<uintptr_t>(p) & 31) == 0;
+}
+
 template <int kEpi>
 __device__ __forceinline__ void epilogue_tile(const GemmArgs& g, uint32_t taddr, int row, int n_blk) {
                 if (kEpi == EPI_SWIGLU) {
                     const int h0 = n_blk * (BN / 2);   // first hidden column of this tile
                     const int hidden = g.N / 2;
+                    const bool w_act = wide_ok(g.C, g.ldc), w_gate = wide_ok(g.C_gate, g.ldc), w_up = wide_ok(g.C_up, g.ldc);
     #pragma unroll 1
                     for (int c = 0; c < BN / 2; c += 32) {
                         uint32_t rg[32], ru[32];
@@ -136,57 +157,57 @@ __device__ __forceinline__ void epilogue_tile(const GemmArgs& g, uint32_t taddr,
                         ptx::tmem_ld32(taddr + BN / 2 + c, ru);
                         ptx::tmem_ld_wait();
                         if (row < g.M) {
+                            bf16x8 oa[4], og[4], ou[4];
     #pragma unroll
                             for (int v = 0; v < 4; ++v) {
-                                const int col = h0 + c + v * 8;
-                                if (col < hidden) {
-                                    float gt[8], up[8], act[8];
+                                float gt[8], up[8], act[8];
     #pragma unroll
-                                    for (int j = 0; j < 8; ++j) {
-                                        gt[j] = round_bf16(__uint_as_float(rg[v * 8 + j]));
-                                        up[j] = round_bf16(__uint_as_float(ru[v * 8 + j]));
-                                        act[j] = round_bf16(gt[j] / (1.f + __expf(-gt[j]))) * up[j];
-                                    }
-                                    const int64_t off = (int64_t)row * g.ldc + col;
-                                    st16(g.C + off, pack8(act));
-                                    if (g.C_gate) st16(g.C_gate + off, pack8(gt));
-                                    if (g.C_up) st16(g.C_up + off, pack8(up));
+                                for (int j = 0; j < 8; ++j) {
+                                    gt[j] = round_bf16(__uint_as_float(rg[v * 8 + j]));
+                                    up[j] = round_bf16(__uint_as_float(ru[v * 8 + j]));
+                                    act[j] = round_bf16(gt[j] / (1.f + __expf(-gt[j]))) * up[j];
                                 }
+                                oa[v] = pack8(act); og[v] = pack8(gt); ou[v] = pack8(up);
                             }
+                            const int64_t off = (int64_t)row * g.ldc + h0 + c;
+                            store_groups(g.C, w_act, off, oa, h0 + c, hidden);
+                            if (g.C_gate) store_groups(g.C_gate, w_gate, off, og, h0 + c, hidden);
+                            if (g.C_up) store_groups(g.C_up, w_up, off, ou, h0 + c, hidden);
                         }
                     }
                 } else {
                     const int n0 = n_blk * BN;
+                    const bool w_c = wide_ok(g.C, g.ldc);
     #pragma unroll 1
                     for (int c = 0; c < BN; c += 32) {
                         uint32_t r[32];
                         ptx::tmem_ld32(taddr + c, r);
                         ptx::tmem_ld_wait();
                         if (row < g.M) {
+                            bf16x8 o[4];
     #pragma unroll
                             for (int v = 0; v < 4; ++v) {
                                 const int col = n0 + c + v * 8;
-                                if (col < g.N) {
-                                    float f[8];
+                                float f[8];
     #pragma unroll
-                                    for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
-                                    if (kEpi == EPI_ROPE && col < g.rot_cols) {
-                                        const int pos = row % g.seq_len;
-                                        const int pair0 = (col % g.head_dim) >> 1;
-                                        const int64_t to = (int64_t)pos * (g.head_dim >> 1) + pair0;
-                                        const float4 cs = *reinterpret_cast<const float4*>(g.cos_t + to);
-                                        const float4 sn = *reinterpret_cast<const float4*>(g.sin_t + to);
-                                        const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
+                                for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
+                                if (kEpi == EPI_ROPE && col < g.rot_cols && col < g.N) {
+                                    const int pos = row % g.seq_len;
+                                    const int pair0 = (col % g.head_dim) >> 1;
+                                    const int64_t to = (int64_t)pos * (g.head_dim >> 1) + pair0;
+                                    const float4 cs = *reinterpret_cast<const float4*>(g.cos_t + to);
+                                    const float4 sn = *reinterpret_cast<const float4*>(g.sin_t + to);
+                                    const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
     #pragma unroll
-                                        for (int j = 0; j < 4; ++j) {
-                                            const float a = round_bf16(f[2 * j]), b = round_bf16(f[2 * j + 1]);
-                                            f[2 * j] = a * cc[j] - b * ss[j];
-                                            f[2 * j + 1] = a * ss[j] + b * cc[j];
-                                        }
+                                    for (int j = 0; j < 4; ++j) {
+                                        const float a = round_bf16(f[2 * j]), b = round_bf16(f[2 * j + 1]);
+                                        f[2 * j] = a * cc[j] - b * ss[j];
+                                        f[2 * j + 1] = a * ss[j] + b * cc[j];
                                     }
-                                    st16(g.C + (int64_t)row * g.ldc + col, pack8(f));
                                 }
+                                o[v] = pack8(f);
                             }
+                            store_groups(g.C, w_c, (int64_t)row * g.ldc + n0 + c, o, n0 + c, g.N);
                         }
                     }
                 }

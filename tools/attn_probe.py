@@ -90,13 +90,15 @@ def run_bwd():
     assert lib.ftl_attn_dbg_read(host) == 0
     which = sys.argv[2] if len(sys.argv) > 2 else "dkv"
     names = {"dkv": ["top", "bar", "Srdy", "Tfree", "ld", "math", "pub", "-", "M.Qld", "M.top", "M.Tseen", "M.iss"],
-             "dq": ["top", "bar", "Srdy", "Tfree", "ld", "math", "pub", "-", "M.Kld", "M.top", "M.Tseen", "M.iss"]}[which]
+             # dq: one row per work ITEM of CTA 0: item start, first S ready, key-tile loop done, next rows requested,
+             # last MMA done, next rows published, epilogue done; last column = key tiles of the item
+             "dq": ["start", "S0rdy", "loopend", "loaded", "accfull", "publ", "epi", "tiles", "e.ld0", "e.st0", "e.ld1", "e.st1"]}[which]
     t0 = min(host[k] for k in range(16) if host[k])
     n = max(t for t in range(64) if host[t * 16]) + 1
     print("iter " + " ".join(f"{x:>7}" for x in names))
     for t in range(n):
-        print(f"{t:4d} " + " ".join(f"{host[t * 16 + k] - t0 if host[t * 16 + k] else -1:7d}" for k in range(len(names))))
-    if n > 6:
+        print(f"{t:4d} " + " ".join(f"{(host[t * 16 + k] - t0 if names[k] != 'tiles' else host[t * 16 + k]) if host[t * 16 + k] else -1:7d}" for k in range(len(names))))
+    if n > 6 and which == "dkv":
         print("cycles per iteration (steady state):", (host[(n - 2) * 16] - host[2 * 16]) / (n - 4))
 
 
