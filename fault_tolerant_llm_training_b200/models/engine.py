@@ -237,6 +237,7 @@ class NativeEngine:
         #   hook_grads(b):  called after the last kernel that writes bucket b's gradients
         self.hook_params = None
         self.hook_grads = None
+        self.sparse_emb_zero, self._emb_dirty = False, None   # see backward(): set by single-rank trainers
         self.hook_params_bwd = None   # called before the backward of bucket b reads its parameters
         self.fused_gather = None      # FSDP: object with qkv(i, x, out) / swiglu(i, x, act, gate, up) running the
                                       # gather-fused GEMMs for layer i (parallel/fsdp.py)
@@ -394,9 +395,19 @@ class NativeEngine:
             dx, spare = spare, dx
             if self.hook_grads is not None:
                 self.hook_grads(i + 1)
-        # embedding: deterministic scatter-add
-        self.g_emb.zero_()
-        sorted_tok, perm = torch.sort(tokens.view(-1), stable=True)
+        # embedding: deterministic scatter-add into a zero table gradient.  The table gradient is 1 GB and only the rows
+        # of this batch's tokens are written, so when nobody else writes into it (single rank: no in-place reduction
+        # of peers' rows) only the rows the PREVIOUS step touched are cleared instead of the whole buffer.
+        flat_tok = tokens.view(-1)
+        if self.sparse_emb_zero and self._emb_dirty is not None:
+            self.g_emb.index_fill_(0, self._emb_dirty, 0)
+        else:
+            self.g_emb.zero_()
+        if self.sparse_emb_zero:
+            if self._emb_dirty is None:
+                self._emb_dirty = torch.empty_like(flat_tok)
+            self._emb_dirty.copy_(flat_tok.clamp(0, self.cfg.vocab_size - 1))   # ids the kernels skip must not index
+        sorted_tok, perm = torch.sort(flat_tok, stable=True)
         N.embedding_bwd(sorted_tok, perm, dx, self.g_emb)
         if self.hook_grads is not None:
             self.hook_grads(0)
@@ -453,6 +464,9 @@ class NativeTrainer:
         if self.engine is not None and (self.engine.B, self.engine.S) == (B, S):
             return
         self.engine = NativeEngine(self.model, self.flat, self.cfg, B, S, self.device)
+        self.engine.sparse_emb_zero = self.env.world_size == 1 and self.parallel != "fsdp"
+        if self.engine.sparse_emb_zero:
+            self.engine.g_emb.zero_()                          # a previous engine (other shape) may have left rows behind
         T = B * S
         nbytes = 2 * T * 8 + 64
         # staging ring: [tokens | labels | inv_n, hyper[8]] packed so that a step needs ONE H2D copy.  The host
