@@ -25,3 +25,23 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
 rows = [(e.key, e.device_time_total / e.count) for e in prof.key_averages() if e.device_time_total > 0]
 for k, t in sorted(rows, key=lambda r: -r[1]):
     print(f"{t:9.1f} us  {k[:90]}")
+
+# the library SDPA measured the same way (back to back, CUPTI kernel times) for a like-for-like comparison
+import torch.nn.functional as F
+x = qkv.view(B, S, H + 2 * KV, hd)
+q, k, v = (t.transpose(1, 2).contiguous().requires_grad_() for t in (x[:, :, :H], x[:, :, H:H + KV], x[:, :, H + KV:]))
+do = dout.view(B, S, H, hd).transpose(1, 2).contiguous()
+def sdpa():
+    o = F.scaled_dot_product_attention(q, k, v, is_causal=True, enable_gqa=True)
+    o.backward(do)
+for _ in range(3):
+    sdpa()
+torch.cuda.synchronize()
+with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    for _ in range(10):
+        sdpa()
+    torch.cuda.synchronize()
+rows = [(e.key, e.device_time_total / e.count, e.count // 10) for e in prof.key_averages() if e.device_time_total > 0]
+print("library SDPA (forward + autograd backward), same method:")
+for k_, t, n in sorted(rows, key=lambda r: -r[1])[:8]:
+    print(f"{t:9.1f} us x{n}  {k_[:90]}")
