@@ -1248,15 +1248,21 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
             const uint4* drow = reinterpret_cast<const uint4*>(a.dout_in + tok * a.ld_do + h2 * HD + half * (HD / 2));
             const uint4* orow = reinterpret_cast<const uint4*>(a.o_in + tok * a.ld_do + h2 * HD + half * (HD / 2));
             delta_idx = ((int64_t)b2 * a.H + h2) * a.S + qt2 * BM + r;
+            // one row per thread: every load instruction of a warp touches 32 different lines, so the count of
+            // instructions is what this costs (~5 900 cycles per item with 16-byte loads): 32-byte loads halve it
+            uint32_t vo[HD / 4];
+#pragma unroll
+            for (int i = 0; i < HD / 32; ++i) {
+                ld_row32(qrow + 2 * i, vq + 8 * i);
+                ld_row32(drow + 2 * i, vd + 8 * i);
+                ld_row32(orow + 2 * i, vo + 8 * i);
+            }
             float dot = 0.f;                                           // this half of delta = sum_d dO * O of the row
 #pragma unroll
             for (int i = 0; i < HD / 16; ++i) {
-                const uint4 x = qrow[i], y = drow[i], z = orow[i];
-                vq[4 * i] = x.x; vq[4 * i + 1] = x.y; vq[4 * i + 2] = x.z; vq[4 * i + 3] = x.w;
-                vd[4 * i] = y.x; vd[4 * i + 1] = y.y; vd[4 * i + 2] = y.z; vd[4 * i + 3] = y.w;
                 float fo[8], fd[8];
-                unpack8(*reinterpret_cast<const bf16x8*>(&z), fo);
-                unpack8(*reinterpret_cast<const bf16x8*>(&y), fd);
+                unpack8(*reinterpret_cast<const bf16x8*>(&vo[4 * i]), fo);
+                unpack8(*reinterpret_cast<const bf16x8*>(&vd[4 * i]), fd);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) dot = fmaf(fo[k], fd[k], dot);
             }
@@ -1496,7 +1502,7 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
                          float* delta, void* dqkv, const float* cos_t, const float* sin_t, float* scratch, int B, int S, int H,
                          int KV, int hd, cudaStream_t stream) {
     if (S % 128 || (hd != 64 && hd != 128) || H % KV || ld_qkv % 16 || ld_out % 16 || ((uintptr_t)dqkv & 31) ||
-        ((uintptr_t)scratch & 31))
+        ((uintptr_t)scratch & 31) || ((uintptr_t)qkv & 31) || ((uintptr_t)out & 31) || ((uintptr_t)d_out & 31))
         return (int)cudaErrorInvalidValue;
     const int64_t T = (int64_t)B * S;
     CUtensorMap tq128, tq64, tdo128, tdo64;

@@ -35,6 +35,11 @@ __device__ __forceinline__ void st_row32(__nv_bfloat16* p, const bf16x8& x, cons
     asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
                  :: "l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w) : "memory");
 }
+// 32-byte load of a row segment owned by one thread: half as many per-line transactions as two 16-byte loads
+__device__ __forceinline__ void ld_row32(const void* p, uint32_t* d) {
+    asm volatile("ld.global.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]) : "l"(p));
+}
 __device__ __forceinline__ void st8f(float* p, const uint32_t* v) {      // 8 fp32 values given as raw bits
     asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
                  :: "l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
