@@ -738,6 +738,26 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnArgs a) {
 }
 
 // inverse rotary embedding of 8 consecutive gradient values (4 pairs) of a q / k row at position pos
+// Same for 16 consecutive values (two groups) with ONE 32-byte load per table: the epilogue threads each own a row
+// (= a position), so every table load of a warp touches 32 different lines and the number of load instructions is what
+// the fused inverse RoPE costs (it added ~30 us per backward kernel at the model shape with 16-byte loads).
+__device__ __forceinline__ void unrope16(float (&f)[8], float (&f2)[8], const AttnArgs& a, int pos, int d0, int hd) {
+    if (!a.cos_t) return;
+    const int64_t to = (int64_t)pos * (hd >> 1) + (d0 >> 1);
+    uint32_t cu[8], su[8];
+    ld_row32(a.cos_t + to, cu);
+    ld_row32(a.sin_t + to, su);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float c0 = __uint_as_float(cu[j]), s0 = __uint_as_float(su[j]);
+        const float c1 = __uint_as_float(cu[4 + j]), s1 = __uint_as_float(su[4 + j]);
+        const float x = f[2 * j], y = f[2 * j + 1], x2 = f2[2 * j], y2 = f2[2 * j + 1];
+        f[2 * j] = x * c0 + y * s0;                // rotation by -angle
+        f[2 * j + 1] = -x * s0 + y * c0;
+        f2[2 * j] = x2 * c1 + y2 * s1;
+        f2[2 * j + 1] = -x2 * s1 + y2 * c1;
+    }
+}
 __device__ __forceinline__ void unrope8(float (&f)[8], const AttnArgs& a, int pos, int d0, int hd) {
     if (!a.cos_t) return;
     const int64_t to = (int64_t)pos * (hd >> 1) + (d0 >> 1);
@@ -1039,8 +1059,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                         fv2[i] = __uint_as_float(v[u * 8 + 8 + i]);
                         fk2[i] = __uint_as_float(kk[u * 8 + 8 + i]) * a.scale;
                     }
-                    unrope8(fk, a, kj, c + u * 8, HD);
-                    unrope8(fk2, a, kj, c + u * 8 + 8, HD);
+                    unrope16(fk, fk2, a, kj, c + u * 8, HD);
                     st_row32(a.out + trow + (a.H + a.KV + g) * HD + c + u * 8, pack8(fv), pack8(fv2));
                     st_row32(a.out + trow + (a.H + g) * HD + c + u * 8, pack8(fk), pack8(fk2));
                 }
@@ -1368,8 +1387,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
                         f[i] = __uint_as_float(v[u * 8 + i]) * a.scale;
                         f2[i] = __uint_as_float(v[u * 8 + 8 + i]) * a.scale;
                     }
-                    unrope8(f, a, qi, c + u * 8, HD);
-                    unrope8(f2, a, qi, c + u * 8 + 8, HD);
+                    unrope16(f, f2, a, qi, c + u * 8, HD);
                     st_row32(orow + c + u * 8, pack8(f), pack8(f2));        // full 32-byte sectors
                 }
                 DQ_DBG(threadIdx.x == 64, item_it, c == 0 ? 9 : 11);
@@ -1502,7 +1520,8 @@ FTL_API int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const
                          float* delta, void* dqkv, const float* cos_t, const float* sin_t, float* scratch, int B, int S, int H,
                          int KV, int hd, cudaStream_t stream) {
     if (S % 128 || (hd != 64 && hd != 128) || H % KV || ld_qkv % 16 || ld_out % 16 || ((uintptr_t)dqkv & 31) ||
-        ((uintptr_t)scratch & 31) || ((uintptr_t)qkv & 31) || ((uintptr_t)out & 31) || ((uintptr_t)d_out & 31))
+        ((uintptr_t)scratch & 31) || ((uintptr_t)qkv & 31) || ((uintptr_t)out & 31) || ((uintptr_t)d_out & 31) ||
+        ((uintptr_t)cos_t & 31) || ((uintptr_t)sin_t & 31))
         return (int)cudaErrorInvalidValue;
     const int64_t T = (int64_t)B * S;
     CUtensorMap tq128, tq64, tdo128, tdo64;

@@ -4,6 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from torch.profiler import profile, ProfilerActivity
 from fault_tolerant_llm_training_b200.ops import native as N
+from fault_tolerant_llm_training_b200.ops import torch_ops as T
 
 B, S, H, KV, hd = 1, 2048, 32, 8, 128
 if len(sys.argv) > 2:
@@ -15,12 +16,13 @@ dout = (torch.randn(B * S, H * hd, device="cuda") * 0.5).to(torch.bfloat16)
 out = torch.empty(B * S, H * hd, device="cuda", dtype=torch.bfloat16)
 lse = torch.empty(B * H * S, device="cuda"); delta = torch.empty_like(lse)
 dqkv = torch.zeros_like(qkv)
+cos, sin = T.rope_table(hd, S, 500000.0, device="cuda")   # the backward un-rotates dq / dk in its epilogues, as in training
 for _ in range(3):
-    N.attn_fwd(qkv, out, lse, B, S, H, KV, hd); N.attn_bwd(qkv, out, dout, lse, delta, dqkv, B, S, H, KV, hd)
+    N.attn_fwd(qkv, out, lse, B, S, H, KV, hd); N.attn_bwd(qkv, out, dout, lse, delta, dqkv, B, S, H, KV, hd, cos, sin)
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(10):
-        N.attn_fwd(qkv, out, lse, B, S, H, KV, hd); N.attn_bwd(qkv, out, dout, lse, delta, dqkv, B, S, H, KV, hd)
+        N.attn_fwd(qkv, out, lse, B, S, H, KV, hd); N.attn_bwd(qkv, out, dout, lse, delta, dqkv, B, S, H, KV, hd, cos, sin)
     torch.cuda.synchronize()
 rows = [(e.key, e.device_time_total / e.count) for e in prof.key_averages() if e.device_time_total > 0]
 for k, t in sorted(rows, key=lambda r: -r[1]):
