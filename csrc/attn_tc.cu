@@ -993,11 +993,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
                             const ulonglong2 lb = *reinterpret_cast<const ulonglong2*>(lse_s + c0 + u * 8 + 4);
                             const ulonglong2 da = *reinterpret_cast<const ulonglong2*>(del_s + c0 + u * 8);
                             const ulonglong2 db = *reinterpret_cast<const ulonglong2*>(del_s + c0 + u * 8 + 4);
-#ifdef FTL_ATTN_NOLDS
-                            const uint64_t nl[4] = {scale2, scale2, scale2, scale2}, nd[4] = {scale2, scale2, scale2, scale2};
-#else
                             const uint64_t nl[4] = {la.x, la.y, lb.x, lb.y}, nd[4] = {da.x, da.y, db.x, db.y};
-#endif
                             uint32_t pp[4], dd[4];
 #pragma unroll
                             for (int k = 0; k < 4; ++k) {
