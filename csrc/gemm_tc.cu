@@ -639,8 +639,8 @@ static int launch_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
     return (int)cudaLaunchKernelEx(&cfg, kern, a, b, a2, b2, g);
 }
 
-// cluster size used by the entry points (FTL_GEMM_CLUSTER=1 falls back to independent CTAs)
-static int gemm_cluster() {
+// cluster size asked for by the environment (FTL_GEMM_CLUSTER=1 falls back to independent CTAs)
+static int gemm_cluster_env() {
     static int c = -1;
     if (c < 0) {
         const char* e = getenv("FTL_GEMM_CLUSTER");
@@ -650,10 +650,31 @@ static int gemm_cluster() {
     return c;
 }
 
+// True when p is ordinary device memory allocated on the GPU that is current now.
+static bool on_this_gpu(const void* p) {
+    if (!p) return true;
+    int dev = -1;
+    cudaPointerAttributes at{};
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeDevice && at.device == dev;
+}
+
+// Cluster size actually used for a call whose B operand(s) are b / b2.  The cluster kernels (2, 4) fetch B with TMA
+// multicast loads.  TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
+// another GPU's memory hung the GPU: any operand that is not plain memory of the current device is routed to the
+// kernel without multicast.
+static int gemm_cluster(const void* b, const void* b2) {
+    const int c = gemm_cluster_env();
+    if (c >= 2 && !(on_this_gpu(b) && on_this_gpu(b2))) return 1;
+    return c;
+}
+
 template <int kEpi, bool kAMn, bool kBMn>
-static int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2, const CUtensorMap& b2,
+static int launch(int c, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2, const CUtensorMap& b2,
                   const GemmArgs& g, int max_ctas, cudaStream_t stream) {
-    const int c = gemm_cluster();
     if (c == 0) return launch_pair<kEpi, kAMn, kBMn>(a, b, a2, b2, g, max_ctas, stream);
     if (c == 1) return launch_c<kEpi, kAMn, kBMn, 1>(a, b, a2, b2, g, max_ctas, stream);
     if (c == 4 && kEpi != EPI_SWIGLU) return launch_c<kEpi, kAMn, kBMn, 4>(a, b, a2, b2, g, max_ctas, stream);
@@ -677,7 +698,8 @@ FTL_API int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, i
     int e;
     e = a_mn ? make_tmap(&ta, a, K, M, lda, 64, BK) : make_tmap(&ta, a, M, K, lda, BK, BM);
     if (e) return e;
-    const int cl = gemm_cluster() == 0 ? 2 : gemm_cluster();
+    const int csel = gemm_cluster(b, K2 > 0 ? b2 : nullptr);
+    const int cl = csel == 0 ? 2 : csel;
     e = b_mn ? make_tmap(&tb, b, K, N, ldb, 64, BK) : make_tmap(&tb, b, N, K, ldb, BK, BN / cl);
     if (e) return e;
     ta2 = ta;
@@ -693,10 +715,10 @@ FTL_API int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, i
     g.ldc = ldc;
     g.M = M; g.N = N; g.K = K + (K2 > 0 ? K2 : 0);
     g.nk1 = (K + BK - 1) / BK;
-    if (!a_mn && !b_mn) return launch<EPI_PLAIN, false, false>(ta, tb, ta2, tb2, g, max_ctas, stream);
-    if (!a_mn && b_mn) return launch<EPI_PLAIN, false, true>(ta, tb, ta2, tb2, g, max_ctas, stream);
-    if (a_mn && b_mn) return launch<EPI_PLAIN, true, true>(ta, tb, ta2, tb2, g, max_ctas, stream);
-    return launch<EPI_PLAIN, true, false>(ta, tb, ta2, tb2, g, max_ctas, stream);
+    if (!a_mn && !b_mn) return launch<EPI_PLAIN, false, false>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
+    if (!a_mn && b_mn) return launch<EPI_PLAIN, false, true>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
+    if (a_mn && b_mn) return launch<EPI_PLAIN, true, true>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
+    return launch<EPI_PLAIN, true, false>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
 }
 
 // gate|up dual GEMM with the SwiGLU epilogue: x [M, K], w1 / w3 [H, K]; writes act (and gate, up if non-null), [M, H].
@@ -713,7 +735,7 @@ FTL_API int ftl_gemm_swiglu(const void* x, int64_t ldx, const void* w1, const vo
     g.ldc = ldo;
     g.M = M; g.N = 2 * H; g.K = K;   // accumulator columns: 128 gate + 128 up per tile; ceil(2H/256) = ceil(H/128) tiles
     g.nk1 = (K + BK - 1) / BK;
-    return launch<EPI_SWIGLU, false, false>(ta, tb, ta, tb2, g, max_ctas, stream);
+    return launch<EPI_SWIGLU, false, false>(gemm_cluster(w1, w3), ta, tb, ta, tb2, g, max_ctas, stream);
 }
 
 // fused QKV projection + RoPE on the first rot_cols output columns (q heads then k heads).
@@ -725,12 +747,13 @@ FTL_API int ftl_gemm_qkv_rope(const void* x, int64_t ldx, const void* wqkv, int6
     CUtensorMap ta, tb;
     int e;
     if ((e = make_tmap(&ta, x, M, K, ldx, BK, BM))) return e;
-    if ((e = make_tmap(&tb, wqkv, N, K, ldw, BK, BN / (gemm_cluster() == 0 ? 2 : gemm_cluster())))) return e;
+    const int csel = gemm_cluster(wqkv, nullptr);
+    if ((e = make_tmap(&tb, wqkv, N, K, ldw, BK, BN / (csel == 0 ? 2 : csel)))) return e;
     GemmArgs g{};
     g.C = (__nv_bfloat16*)qkv; g.ldc = ldo;
     g.M = M; g.N = N; g.K = K; g.nk1 = (K + BK - 1) / BK;
     g.cos_t = cos_t; g.sin_t = sin_t; g.seq_len = seq_len; g.head_dim = head_dim; g.rot_cols = rot_cols;
-    return launch<EPI_ROPE, false, false>(ta, tb, ta, tb, g, max_ctas, stream);
+    return launch<EPI_ROPE, false, false>(csel, ta, tb, ta, tb, g, max_ctas, stream);
 }
 
 
@@ -740,7 +763,7 @@ FTL_API int ftl_gemm_qkv_rope(const void* x, int64_t ldx, const void* wqkv, int6
 // assembled in `wqkv` / `w1`, `w3` (local staging) while the MMAs run.  scratch: >= 1 + n_mat * rows/128 ints.
 static int gather_setup(GemmArgs& g, const void* const* peer_shards, int nmat, void* dst0, void* dst1, int64_t off0,
                         int64_t off1, int rows, int rows_per_rank, int rank, int world, int* scratch, cudaStream_t stream) {
-    if (gemm_cluster() != 0 || rows_per_rank % 128 || rows % 128 || rows_per_rank * world != rows) return (int)cudaErrorInvalidValue;
+    if (gemm_cluster_env() != 0 || rows_per_rank % 128 || rows % 128 || rows_per_rank * world != rows) return (int)cudaErrorInvalidValue;
     const int halves = rows / 128;
     cudaError_t e = cudaMemsetAsync(scratch, 0, sizeof(int) * (1 + nmat * halves), stream);
     if (e != cudaSuccess) return (int)e;
