@@ -84,34 +84,23 @@ def _dist_max(value: float, device) -> float:
     return value
 
 
-def run_ours(a) -> dict:
+def _measure_ours(a, env, cfg, tok, data, parallel: str, ckpt: bool) -> dict:
+    """Build one trainer in `parallel` mode and time it: K device-timed steps, K end-to-end steps, and (ckpt) the
+    SIGUSR1 -> durable checkpoint -> resume path.  Everything the trainer allocated is released afterwards."""
+    import gc
+
     import torch
 
-    from fault_tolerant_llm_training_b200.config import ModelConfig
     from fault_tolerant_llm_training_b200.data.datasets import BatchStream, CollatorForCLM, ParquetDataset
-    from fault_tolerant_llm_training_b200.data.synthetic import write_synthetic_parquet
-    from fault_tolerant_llm_training_b200.data.tokenizer import OfflineTokenizer
     from fault_tolerant_llm_training_b200.ops import native as N
-    from fault_tolerant_llm_training_b200.parallel.env import init_dist
     from fault_tolerant_llm_training_b200.trainer import make_trainer
 
-    env = init_dist("cuda")
-    if env.world_size != a.gpus:
-        raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={env.world_size}: launch with torch.distributed.run")
-    cfg = ModelConfig(seq_len=a.seq, vocab_size=131072)  # defaults = train.py:43-53
-    if a.layers:
-        cfg.n_layers = a.layers  # debugging only; reported in config and flagged as not the named model
-    tok = OfflineTokenizer(cfg.vocab_size)
-    data = a.data or "/tmp/ftl_bench/data.parquet"
-    if env.is_main and not os.path.exists(data):
-        write_synthetic_parquet(data, num_docs=64, min_len=a.seq + 64, max_len=a.seq + 512, vocab_size=cfg.vocab_size)
-    env.barrier()
-    total = a.warmup + 2 * a.steps + 8
+    total = a.warmup + 2 * a.steps + 16
     ds = ParquetDataset(data, tok, a.seq, a.batch * total * env.world_size * 2)
     stream = BatchStream(ds, a.batch, CollatorForCLM(a.seq, tok.pad_token_id), rank=env.rank,
                          world_size=env.world_size, pin_memory=True)
     trainer = make_trainer(cfg, env, dtype=torch.bfloat16, lr=5e-5, warmup_steps=100, grad_max_norm=1.0,
-                           clip_mode="clip", seed=0, parallel=a.parallel)
+                           clip_mode="clip", seed=0, parallel=parallel, keep_shards=True, consolidate=False)
     sampler = ClockSampler(env.local_rank)
 
     def sync():
@@ -157,32 +146,126 @@ def run_ours(a) -> dict:
     sampler.stop()
 
     tokens = a.batch * a.seq * env.world_size * a.steps
-    value = tokens / (dev_ms / 1e3)
+    res = {"value": round(tokens / (dev_ms / 1e3), 1), "ms_per_step": round(dev_ms / a.steps, 3),
+           "parallel": trainer.parallel, "clocks": sampler.summary(), "gpu_launches": int(gpu_launches),
+           "loss": round(float(loss_dev), 4)}
+    if e2e_ms is not None:
+        res["e2e"] = {"value": round(tokens / (e2e_ms / 1e3), 1), "unit": "tokens/s",
+                      "ms_per_step": round(e2e_ms / a.steps, 3),
+                      "h2d_bytes_per_step": int(trainer.h2d_bytes_per_step),
+                      "d2h_bytes_per_step": int(trainer.d2h_bytes_per_step), "loss": round(float(loss_e2e), 4)}
+    if ckpt:
+        res.update(_measure_checkpoint(trainer, env, stream))
+    stream.close()
+    trainer.close()
+    del trainer, stream, last, fixed
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res
+
+
+def _measure_checkpoint(trainer, env, stream) -> dict:
+    """The second half of BASELINE.json's metric.  A real SIGUSR1 is delivered to every rank while the step loop of
+    train_loop.py runs (flag-setting handler, cross-rank agreement at the step boundary, drain, sharded save); the
+    clock stops when the manifest is fsynced (= the job may be resubmitted), max over ranks.  `resume_s` is reading
+    that checkpoint back into the device buffers.  Reference: utils.py:65-90 (34.1 s in its own log)."""
+    import shutil
+    import signal
+
+    import torch
+
+    from fault_tolerant_llm_training_b200.ckpt.layout import load_checkpoint
+    from fault_tolerant_llm_training_b200.ft.signals import STOP_NONE, SignalFlags
+
+    path, jobid = "/tmp/ftl_bench/ckpt", "bench"
+    if env.is_main:
+        shutil.rmtree(path, ignore_errors=True)
+        os.makedirs(path, exist_ok=True)
+    env.barrier()
+    torch.cuda.synchronize()
+    flags = SignalFlags().install()
+    t_sig, step = None, 0
+    try:
+        while True:
+            if step == 3:
+                t_sig = time.perf_counter()
+                os.kill(os.getpid(), signal.SIGUSR1)
+            inputs, labels = next(stream)
+            code, n_items = env.step_sync(flags.poll(), int(labels.ne(-100).sum()))
+            if code != STOP_NONE:
+                break
+            trainer.step(inputs, labels, n_items=n_items)
+            step += 1
+        trainer.drain()
+        data_state = env.gather_objects(stream.state_dict()) if env.distributed else stream.state_dict()
+        trainer.save_fn()(path, jobid, trainer.model, trainer.optimizer, trainer.lr_scheduler, step,
+                          data_state=data_state, rank=env.rank, world_size=env.world_size)
+        durable_s = _dist_max(time.perf_counter() - t_sig, env.device)
+    finally:
+        flags.uninstall()
+    tm = dict(trainer.checkpointer.timings)
+    env.barrier()
+    t0 = time.perf_counter()
+    ck = load_checkpoint(path, jobid)
+    trainer.load_state(ck)
+    torch.cuda.synchronize()
+    resume_s = _dist_max(time.perf_counter() - t0, env.device)
+    env.barrier()
+    if env.is_main:
+        shutil.rmtree(path, ignore_errors=True)
+    return {"sigusr1_to_durable_s": round(durable_s, 3), "resume_s": round(resume_s, 3),
+            "ckpt": {"bytes_per_rank": int(tm.get("bytes_this_rank", 0)), "d2h_s": round(tm.get("d2h_s", 0.0), 3),
+                     "write_s": round(tm.get("write_s", 0.0), 3), "fsync_s": round(tm.get("fsync_s", 0.0), 3),
+                     "what": "SIGUSR1 to every rank inside the step loop -> step-boundary agreement -> drain -> sharded "
+                             "snapshot -> manifest fsynced; resume_s = shards -> device buffers"}}
+
+
+def run_ours(a) -> dict:
+    from fault_tolerant_llm_training_b200.config import ModelConfig
+    from fault_tolerant_llm_training_b200.data.synthetic import write_synthetic_parquet
+    from fault_tolerant_llm_training_b200.data.tokenizer import OfflineTokenizer
+    from fault_tolerant_llm_training_b200.parallel.env import init_dist
+
+    env = init_dist("cuda")
+    if env.world_size != a.gpus:
+        raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={env.world_size}: launch with torch.distributed.run")
+    cfg = ModelConfig(seq_len=a.seq, vocab_size=131072)  # defaults = train.py:43-53
+    if a.layers:
+        cfg.n_layers = a.layers  # debugging only; reported in config and flagged as not the named model
+    tok = OfflineTokenizer(cfg.vocab_size)
+    data = a.data or "/tmp/ftl_bench/data.parquet"
+    if env.is_main and not os.path.exists(data):
+        write_synthetic_parquet(data, num_docs=64, min_len=a.seq + 64, max_len=a.seq + 512, vocab_size=cfg.vocab_size)
+    env.barrier()
+    main_mode = a.parallel if a.parallel != "auto" else ("dp" if env.world_size > 1 else "none")
+    r = _measure_ours(a, env, cfg, tok, data, main_mode, ckpt=not a.no_ckpt)
     out = {
-        "metric": METRIC, "value": round(value, 1), "unit": "tokens/s", "n_gpus": env.world_size, "steps": a.steps,
-        "warmup": a.warmup, "ms_per_step": round(dev_ms / a.steps, 3), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": round(value / BASELINE_TOKENS_PER_S, 3), "dtype": "bf16",
+        "metric": METRIC, "value": r["value"], "unit": "tokens/s", "n_gpus": env.world_size, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": round(r["value"] / BASELINE_TOKENS_PER_S, 3), "dtype": "bf16",
         "data": "synthetic parquet (offline word-hash tokenizer, vocab 131072), random-init weights",
         "impl": "ours",
         "config": {"model": "reference train.py:43-53 Llama-style decoder, 8.05B params (dim 4096, 32 layers, "
                             "32 heads / 8 kv heads, ffn 14336, vocab 131072)" if not a.layers else
                             f"DEBUG {cfg.n_layers}-layer cut of the named model (not a valid bench)",
                    "global_batch": a.batch * env.world_size, "seq_len": a.seq,
-                   "parallelism": ("single" if env.world_size == 1 else f"{trainer.parallel}{env.world_size}"),
+                   "parallelism": ("single" if env.world_size == 1 else f"{r['parallel']}{env.world_size}"),
                    "optimizer": "AdamW fused, bf16 states, grad clip 1.0", "params": cfg.num_params(),
                    "kernels": {"gemm": os.environ.get("FTL_GEMM", "tc") + " (tc = own tcgen05 CTA-pair kernel)",
                                "attention": os.environ.get("FTL_ATTN", "tc") + " (tc = own tcgen05 flash attention, deterministic)"},
                    "l2": "no flush: each step streams >64 GB of weights/grads/moments, far larger than the 126 MB L2"},
-        "clocks": sampler.summary(), "gpu_launches": int(gpu_launches),
-        "loss": round(float(loss_dev), 4),
+        "clocks": r["clocks"], "gpu_launches": r["gpu_launches"], "loss": r["loss"],
     }
-    if e2e_ms is not None:
-        out["e2e"] = {"value": round(tokens / (e2e_ms / 1e3), 1), "unit": "tokens/s",
-                      "ms_per_step": round(e2e_ms / a.steps, 3),
-                      "h2d_bytes_per_step": int(trainer.h2d_bytes_per_step),
-                      "d2h_bytes_per_step": int(trainer.d2h_bytes_per_step), "loss": round(float(loss_e2e), 4)}
-    stream.close()
-    trainer.close()
+    for k in ("e2e", "sigusr1_to_durable_s", "resume_s", "ckpt"):
+        if k in r:
+            out[k] = r[k]
+    # N > 1: the fully-sharded engine on the same job, so that one stock command records both modes (BASELINE config 4)
+    if env.world_size > 1 and a.parallel == "auto" and not a.no_fsdp:
+        f = _measure_ours(a, env, cfg, tok, data, "fsdp", ckpt=not a.no_ckpt)
+        out["fsdp"] = {k: f[k] for k in ("value", "ms_per_step", "e2e", "gpu_launches", "loss", "sigusr1_to_durable_s",
+                                         "resume_s") if k in f}
+        out["fsdp"]["unit"] = "tokens/s"
+        out["fsdp"]["parallelism"] = f"fsdp{env.world_size}"
     env.shutdown()
     return out if env.is_main else {}
 
@@ -205,32 +288,58 @@ def run_reference(a) -> dict:
         while not os.path.exists(data):
             time.sleep(0.2)
     dev = torch.device(f"cuda:{local_rank}")
-    sampler = ClockSampler(local_rank)
-    # device-timed value: the stock logging frequency of the reference (5; train.sh does not override it)
-    r = H.run_reference(world, a.steps, a.warmup, a.seq, a.batch, 5, data, sampler)
-    dev_ms = _dist_max(r["device_ms"], dev)
-    e2e_ms = None
-    if not a.no_e2e:
-        # end to end: same loop with the loss read on the host every step (--logging-frequency 1)
-        r2 = H.run_reference(world, a.steps, a.warmup, a.seq, a.batch, 1, data, None)
-        e2e_ms = _dist_max(r2["wall_ms"], dev)
     tokens = a.batch * a.seq * world * a.steps
-    value = tokens / (dev_ms / 1e3)
+
+    def one(mode: str, ckpt: bool) -> dict:
+        sampler = ClockSampler(local_rank)
+        # ONE call of the reference's train(): W warm-up steps, K device-timed steps at the stock logging frequency
+        # (5; train.sh does not override it), then K end-to-end steps with the loss read on the host every step
+        r = H.run_reference(world, a.steps, a.warmup, a.seq, a.batch, data, sampler, mode=mode, e2e=not a.no_e2e,
+                            ckpt_timing=ckpt)
+        dev_ms = _dist_max(r["device_ms"], dev)
+        res = {"value": round(tokens / (dev_ms / 1e3), 1), "ms_per_step": round(dev_ms / a.steps, 3),
+               "clocks": sampler.summary()}
+        if "wall_ms" in r:
+            e2e_ms = _dist_max(r["wall_ms"], dev)
+            res["e2e"] = {"value": round(tokens / (e2e_ms / 1e3), 1), "unit": "tokens/s",
+                          "ms_per_step": round(e2e_ms / a.steps, 3), "h2d_bytes_per_step": 2 * a.batch * a.seq * 8,
+                          "d2h_bytes_per_step": 4}
+        if "sigusr1_to_durable_s" in r:
+            res["sigusr1_to_durable_s"] = round(r["sigusr1_to_durable_s"], 3)
+            res["resume_s"] = round(r["resume_load_s"], 3)
+            res["ckpt"] = {"bytes_per_rank": int(r["ckpt_bytes"]),
+                           "what": "SIGUSR1 to the process inside train() -> catch_SIG_exception -> handle_exit -> "
+                                   "torch.save returned (utils.py:65-90; not fsynced); resume_s = torch.load(map_location="
+                                   "'cpu') of that file only (train.py:22)"}
+        return res
+
+    main_mode = "ddp" if a.parallel in ("auto", "dp", "none") else "fsdp"
+    # the reference's exit handler has no rank guard (every rank would torch.save the full 48 GB state): its
+    # checkpoint time is measured on the single-process run, which is also what rank 0 of a DDP job would pay
+    r = one(main_mode, ckpt=(world == 1 and not a.no_ckpt))
     out = {
-        "metric": METRIC, "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": a.steps,
-        "warmup": a.warmup, "ms_per_step": round(dev_ms / a.steps, 3), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": round(value / BASELINE_TOKENS_PER_S, 3), "dtype": "bf16",
+        "metric": METRIC, "value": r["value"], "unit": "tokens/s", "n_gpus": world, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": round(r["value"] / BASELINE_TOKENS_PER_S, 3), "dtype": "bf16",
         "data": "synthetic parquet (offline word-hash tokenizer shim, vocab 131072), random-init weights",
         "impl": "reference",
         "config": {"model": "reference train.py:43-53 Llama-style decoder, 8.05B params", "global_batch": a.batch * world,
-                   "seq_len": a.seq, "parallelism": "single" if world == 1 else f"torch DDP x{world} around the reference model",
+                   "seq_len": a.seq,
+                   "parallelism": "single" if world == 1 else f"torch {main_mode.upper()} x{world} around the reference model",
                    "optimizer": "torch.optim.AdamW (foreach), as train.py:68"},
-        "clocks": sampler.summary(), "gpu_launches": 0,
+        "clocks": r["clocks"], "gpu_launches": 0,
     }
-    if e2e_ms is not None:
-        out["e2e"] = {"value": round(tokens / (e2e_ms / 1e3), 1), "unit": "tokens/s",
-                      "ms_per_step": round(e2e_ms / a.steps, 3), "h2d_bytes_per_step": 2 * a.batch * a.seq * 8,
-                      "d2h_bytes_per_step": 4}
+    for k in ("e2e", "sigusr1_to_durable_s", "resume_s", "ckpt"):
+        if k in r:
+            out[k] = r[k]
+    if world > 1 and a.parallel == "auto" and not a.no_fsdp:
+        try:
+            f = one("fsdp", ckpt=False)
+            out["fsdp"] = {k: f[k] for k in ("value", "ms_per_step", "e2e") if k in f}
+            out["fsdp"]["unit"] = "tokens/s"
+            out["fsdp"]["parallelism"] = f"torch FSDP2 (fully_shard per TransformerBlock) x{world} around the reference model"
+        except Exception as e:  # noqa: BLE001 — the DDP numbers above stay valid
+            out["fsdp"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
     return out if rank == 0 else {}
 
 
@@ -245,6 +354,8 @@ def main() -> None:
     p.add_argument("--parallel", default="auto", choices=["auto", "none", "dp", "fsdp"])
     p.add_argument("--data", default="")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-ckpt", action="store_true", help="skip the SIGUSR1 -> durable checkpoint -> resume timing")
+    p.add_argument("--no-fsdp", action="store_true", help="N > 1: do not add the fully-sharded run to the JSON line")
     p.add_argument("--layers", type=int, default=0, help="debug: fewer layers (result is flagged invalid)")
     a = p.parse_args()
     if a.warmup < 3:
