@@ -105,9 +105,10 @@ def load_checkpoint(checkpoint_path: str, checkpoint_id: str) -> Dict[str, Any]:
     """torch.load to CPU (reference: train.py:22)."""
     path = checkpoint_file(checkpoint_path, checkpoint_id)
     if not os.path.exists(path):
-        # a job killed while consolidating leaves only the (durable) shard directory: resume from it
-        from .sharded import MANIFEST, load_sharded, shard_dir
-        d = shard_dir(checkpoint_path, checkpoint_id)
-        if os.path.exists(os.path.join(d, MANIFEST)):
+        # a job killed while consolidating (or while replacing an older checkpoint of the same id) leaves only
+        # durable shard directories: resume from the complete one with the largest training_step
+        from .sharded import best_shard_dir, load_sharded
+        d = best_shard_dir(checkpoint_path, checkpoint_id)
+        if d is not None:
             return load_sharded(d)
     return torch.load(path, map_location="cpu", weights_only=False)

@@ -14,6 +14,13 @@ Save path (SIGUSR1 / exception; BASELINE.json "fault-tolerance subsystem rebuilt
 Resume prefers the consolidated file and falls back to the shard directory (a job killed while
 consolidating loses nothing).  Shards can be read back into a different world size: the manifest maps
 flat-buffer ranges to (file, offset).
+
+Replacing an older checkpoint of the same job id (periodic saves, a second signal) is crash-safe: the new shards
+are written into `checkpoint_<JOBID>.shards.new`; only when its manifest is durable is a stale consolidated file
+of that id unlinked and the directory swapped in (`.shards` -> `.shards.old`, `.shards.new` -> `.shards`).  The
+loader looks at all three names and takes the complete one with the largest training_step, so a kill at any point
+of that sequence leaves a resumable checkpoint.  Shards that a resubmitted job may be reading are never deleted by
+the job that wrote them: the successor removes them once its own first checkpoint is durable.
 """
 from __future__ import annotations
 
@@ -35,6 +42,20 @@ ALIGN = 4096
 
 def shard_dir(checkpoint_path: str, jobid: str) -> str:
     return os.path.join(checkpoint_path, f"checkpoint_{jobid}.shards")
+
+
+def best_shard_dir(checkpoint_path: str, jobid: str) -> Optional[str]:
+    """The complete shard directory (manifest present and readable) of this id with the largest training_step among
+    `.shards`, `.shards.new` (a save that was killed before the swap) and `.shards.old` (killed inside the swap)."""
+    base, best, best_step = shard_dir(checkpoint_path, jobid), None, -1
+    for d in (base, base + ".new", base + ".old"):
+        try:
+            step = int(read_manifest(d)["training_step"])
+        except (OSError, ValueError, KeyError):
+            continue
+        if step > best_step:
+            best, best_step = d, step
+    return best
 
 
 def _fsync_dir(d: str) -> None:
@@ -66,6 +87,7 @@ class FlatCheckpointer:
         self.keep_shards, self.do_consolidate, self.io_threads = keep_shards, consolidate, io_threads
         self.timings: Dict[str, float] = {}
         self._pending: Optional[Tuple[str, str, str]] = None
+        self.predecessor: Optional[Tuple[str, str]] = None   # (checkpoint_path, id) this job resumed from
         N.ckpt_init(256 << 20)  # staging is allocated up front: the exit path must not depend on free memory
 
     # -- save ---------------------------------------------------------------------------------------------------
@@ -75,10 +97,10 @@ class FlatCheckpointer:
         env = t.env
         t0 = time.perf_counter()
         torch.cuda.synchronize()   # the step that was running has retired; buffers are at a step boundary
-        d = shard_dir(checkpoint_path, jobid)
+        final = shard_dir(checkpoint_path, jobid)
+        d = final + ".new"          # written here; swapped in only after its manifest is durable
         if env.is_main:
-            if os.path.isdir(d):
-                shutil.rmtree(d)
+            shutil.rmtree(d, ignore_errors=True)
             os.makedirs(d, exist_ok=True)
         env.barrier()
         segs, my_entries, off = [], [], 0
@@ -108,7 +130,21 @@ class FlatCheckpointer:
             }
             _atomic_json(manifest, os.path.join(d, MANIFEST))
             _fsync_dir(d)
+            # durable from here on (the loader accepts `.shards.new`).  Now retire what it replaces: first a stale
+            # consolidated file of this id (the loader prefers a .ckpt), then swap the directory in.
+            stale = checkpoint_file(checkpoint_path, jobid)
+            if os.path.exists(stale):
+                os.unlink(stale)
+            old = final + ".old"
+            shutil.rmtree(old, ignore_errors=True)
+            if os.path.isdir(final):
+                os.rename(final, old)
+            os.rename(d, final)
+            _fsync_dir(checkpoint_path)
+            shutil.rmtree(old, ignore_errors=True)
+            self._drop_predecessor(logger)
         env.barrier()
+        d = final
         t_durable = time.perf_counter() - t0
         self.timings = {"shards_s": t_shards, "durable_s": t_durable, "d2h_s": io["d2h_s"], "write_s": io["write_s"],
                         "fsync_s": io["fsync_s"], "bytes_this_rank": sum(s[1] for s in segs)}
@@ -119,8 +155,22 @@ class FlatCheckpointer:
         self._pending = (d, checkpoint_file(checkpoint_path, jobid), jobid)
         return d
 
+    def _drop_predecessor(self, logger=None) -> None:
+        """This job's own checkpoint is durable: the shards of the checkpoint it resumed from are no longer needed
+        by anyone, provided the job that wrote them has finished consolidating (its .ckpt exists)."""
+        if self.predecessor is None:
+            return
+        path, rid = self.predecessor
+        if os.path.exists(checkpoint_file(path, rid)):
+            base = shard_dir(path, rid)
+            for dd in (base, base + ".new", base + ".old"):
+                shutil.rmtree(dd, ignore_errors=True)
+            self.predecessor = None
+
     # -- consolidate (rank 0, after the resubmit) ---------------------------------------------------------------
-    def finalize(self, logger=None) -> Optional[str]:
+    def finalize(self, logger=None, resubmitted: bool = False) -> Optional[str]:
+        """resubmitted: a successor job was started and may be reading the shards right now — they are left in place
+        (the successor removes them after its own first durable checkpoint)."""
         if self._pending is None:
             return None
         d, out, _ = self._pending
@@ -132,7 +182,7 @@ class FlatCheckpointer:
             if logger is not None:
                 logger.info(f"[EXIT HANDLER] consolidated reference-layout file written in "
                             f"{time.perf_counter() - t0:.2f} s -> {out}")
-            if not self.keep_shards:
+            if not self.keep_shards and not resubmitted:
                 shutil.rmtree(d, ignore_errors=True)
         self.t.env.barrier()
         return path

@@ -228,6 +228,36 @@ class BatchStream:
         if self.packed and "dataset" in state:
             self.dataset.load_state_dict(state["dataset"])
 
+    def restore(self, saved) -> None:
+        """Restore from what a checkpoint holds: one state (single process) or the list of all ranks' states.
+
+        Same world size and batch size: this rank's own state.  A different geometry is accepted only where the
+        position can be converted exactly — padded mode, where batch i of rank r is a fixed slice of the global
+        sample order: samples consumed = batches * B_old * W_old must be a whole number of new global batches.
+        Packed mode strides documents by rank and carries a per-rank token buffer, so it cannot be re-cut:
+        refused with a clear error rather than silently skipping or repeating samples."""
+        states = saved if isinstance(saved, list) else [saved]
+        w_old = int(states[0].get("world_size", len(states)))
+        b_old = int(states[0].get("batch_size", self.batch_size))
+        if w_old == self.world_size and b_old == self.batch_size and len(states) > (self.rank if len(states) > 1 else 0):
+            self.load_state_dict(states[self.rank] if len(states) > 1 else states[0])
+            return
+        kind = states[0].get("kind", "padded")
+        if self.packed or kind == "packed":
+            raise ValueError(f"checkpoint was written by {w_old} rank(s) at batch size {b_old} with the packed dataset; "
+                             f"its position cannot be converted to {self.world_size} rank(s) at batch size "
+                             f"{self.batch_size} (resume with the original geometry or use --dataset-type padded)")
+        consumed = {int(st["batches_consumed"]) for st in states}
+        if len(consumed) != 1:
+            raise ValueError(f"ranks of the checkpoint disagree on the data position: {sorted(consumed)}")
+        samples = consumed.pop() * b_old * w_old
+        g_new = self.batch_size * self.world_size
+        if samples % g_new:
+            raise ValueError(f"checkpoint consumed {samples} samples ({w_old} rank(s) x batch {b_old}); that is not a "
+                             f"whole number of global batches of {g_new} ({self.world_size} rank(s) x batch {self.batch_size})")
+        self.close()
+        self.batches_consumed = samples // g_new
+
     def rewind(self, batches_consumed: int) -> None:
         """Move the position back to just before batch `batches_consumed` (a step that was fetched but whose
         update never committed).  Padded mode is O(1); packed mode restores the recorded dataset state."""

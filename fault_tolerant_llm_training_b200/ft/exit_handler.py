@@ -75,8 +75,10 @@ def handle_exit(model, optimizer, lr_scheduler, training_step, checkpoint_path, 
         else:
             next_id = resume_id
             info(f"[EXIT HANDLER] No step completed in this job; keeping checkpoint {resume_id}")
+        resubmitted = False
         if type == 10 and rank == 0:
             ret = resubmit(next_id, resubmit_cmd, logger)
+            resubmitted = ret == 0
             if ret != 0:
                 info(f"[EXIT HANDLER] Failed to requeue job {jid}.")
             else:
@@ -84,7 +86,11 @@ def handle_exit(model, optimizer, lr_scheduler, training_step, checkpoint_path, 
         if saved_path is not None and finalize_fn is not None:
             # work that may run after the job has been resubmitted (sharded engines consolidate the shards into
             # the reference-layout file here); the checkpoint was already durable when save_fn returned
-            finalize_fn(logger=logger)
+            import inspect
+            if "resubmitted" in inspect.signature(finalize_fn).parameters:
+                finalize_fn(logger=logger, resubmitted=resubmitted)
+            else:
+                finalize_fn(logger=logger)
     else:
         info(f"[EXIT HANDLER] Unknown exit signal {type}, terminating.")
     return saved_path

@@ -75,8 +75,7 @@ def train(args) -> None:
     if checkpoint is not None:
         states = checkpoint.get("data_state")
         if states is not None:
-            st = states[env.rank] if isinstance(states, list) else states
-            stream.load_state_dict(st)
+            stream.restore(states)   # validates world size / batch size against the checkpoint (or converts, padded mode)
         else:  # file written by the reference: position = training_step batches (train.py:36-39)
             stream.fast_forward(int(checkpoint["training_step"]))
 
@@ -93,6 +92,9 @@ def train(args) -> None:
                     "`--compile` ignored: the B200 engine runs hand-written kernels, not a traced graph")
     if checkpoint is not None:
         trainer.load_state(checkpoint)
+        if hasattr(trainer, "checkpointer"):
+            # its shards may still be read by nobody but us from now on: removed after OUR first durable checkpoint
+            trainer.checkpointer.predecessor = (args.checkpoint_path, args.checkpoint_id)
         logger.info("Model loaded from checkpoint")
         logger.info("Optimizer loaded from checkpoint")
         logger.info("LR Scheduler loaded from checkpoint")
@@ -125,6 +127,12 @@ def train(args) -> None:
             if inject_rank_error == (env.rank, training_step):
                 raise RuntimeError(f"injected rank-local failure on rank {env.rank} at step {training_step}")
             if args.checkpoint_every and training_step > first_step and training_step % args.checkpoint_every == 0:
+                # the save is a sequence of host collectives: agree first, so that a rank that failed on its own
+                # meets a step_sync here and not a gather it can never pair with
+                code, _ = env.step_sync(flags.poll(), 0)
+                if code != STOP_NONE:
+                    agreed = True
+                    raise TrainingInterrupt(stop_code_to_error_type(code))
                 _save_now(trainer, args, training_step, stream, env)
                 logger.info(f"Periodic checkpoint saved at step {training_step}")
 
@@ -148,6 +156,14 @@ def train(args) -> None:
                             f"grad_norm {float(trainer.last_grad_norm):.4f}")
                 t_window, window_steps = time.perf_counter(), 0
             training_step += 1
+        # One more agreement after the last step: a rank that fails locally during its final step (or while its peers
+        # are already past the loop) pairs its step_sync(STOP_ERROR) with this one instead of hanging on a collective
+        # that nobody else enters.
+        # (Signals of this rank are not offered here: a timeout signal that arrives after the last step changes nothing.)
+        code, _ = env.step_sync(STOP_NONE, 0)
+        if code != STOP_NONE:
+            agreed = True
+            raise TrainingInterrupt(stop_code_to_error_type(code))
         logger.info("Training completed")
         if args.save_final:
             _save_now(trainer, args, training_step, stream, env)
