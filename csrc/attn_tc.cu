@@ -38,6 +38,7 @@
 #include <type_traits>
 
 #include "common/ptx.cuh"
+#include "common/tmap_cache.cuh"
 #include "common/util.cuh"
 
 namespace ftl {
@@ -1404,25 +1405,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV64, const AttnArgs a
 }
 
 // ------------------------------------------------------------------------------------------------------- host
-static PFN_cuTensorMapEncodeTiled_v12000 g_attn_encode = nullptr;
-static std::once_flag g_attn_once;
-static void attn_load_encode() {
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-        g_attn_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
-}
+// bf16 [rows, cols] (ld elements), box {64 columns, box_rows}; encoded once per key and cached
 static int attn_tmap(CUtensorMap* out, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
-    std::call_once(g_attn_once, attn_load_encode);
-    if (!g_attn_encode) return (int)cudaErrorNotSupported;
-    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
-    cuuint32_t es[2] = {1, 1};
-    CUresult r = g_attn_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+    return g_tmaps.get(out, ptr, rows, cols, ld, 64, box_rows);
 }
 
 template <typename K>

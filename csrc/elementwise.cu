@@ -99,6 +99,98 @@ __global__ void embedding_bwd_kernel(const int64_t* __restrict__ sorted, const i
     }
 }
 
+// Embedding backward without a sort (replaces torch.sort + embedding_bwd_kernel + the index_fill that cleared the
+// previous step's rows — the last library kernels of the step).  CTA t handles token position t:
+//   * it is the OWNER of row id = tokens[t] iff no earlier position holds the same id; the owner adds the dout rows of
+//     every position with that id in ascending position order (fp32, deterministic) and writes the row once;
+//   * with `prev` (the ids of the previous step, whose rows are the only non-zero rows of the table gradient), CTAs
+//     [T, 2T) clear the rows that the previous step wrote and this step does not write.
+// The scan over positions is a block-cooperative ballot per 128 positions: T^2 / 128 compare rounds in total, a few
+// microseconds at T = 2048.  sumsq (optional, [T]): sum of squares of the bf16 row the owner stored, 0 elsewhere.
+constexpr int kEmbThreads = 128, kEmbVec = 4;
+
+__global__ void __launch_bounds__(kEmbThreads)
+embedding_bwd_direct_kernel(const int64_t* __restrict__ tokens, const int64_t* __restrict__ prev,
+                            const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ dtable, int T, int dim,
+                            int vocab, float* __restrict__ sumsq) {
+    __shared__ unsigned masks[kEmbThreads / 32];
+    __shared__ float red[33];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nvec = dim >> 3;
+    if ((int)blockIdx.x >= T) {
+        // ---- clear a row that only the previous step touched
+        const int t = blockIdx.x - T;
+        const int64_t id = prev[t];
+        if (id < 0 || id >= vocab) return;
+        bool hit = false;
+        for (int j = tid; j < t; j += kEmbThreads) hit |= prev[j] == id;        // an earlier position clears it
+        for (int j = tid; j < T; j += kEmbThreads) hit |= tokens[j] == id;      // this step's owner overwrites it
+        if (__syncthreads_or(hit)) return;
+        bf16x8 z;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) z.v[k] = __floats2bfloat162_rn(0.f, 0.f);
+        for (int i = tid; i < nvec; i += kEmbThreads) st8(dtable + id * dim + i * 8, z);
+        return;
+    }
+    const int t = blockIdx.x;
+    const int64_t id = tokens[t];
+    bool dup = id < 0 || id >= vocab;
+    for (int j = tid; j < t; j += kEmbThreads) dup |= tokens[j] == id;
+    if (__syncthreads_or(dup)) {
+        if (sumsq && tid == 0) sumsq[t] = 0.f;
+        return;
+    }
+    float ss = 0.f;
+    for (int i0 = 0; i0 < nvec; i0 += kEmbVec * kEmbThreads) {
+        float acc[kEmbVec][8];
+#pragma unroll
+        for (int k = 0; k < kEmbVec; ++k)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
+        for (int c = (t / kEmbThreads) * kEmbThreads; c < T; c += kEmbThreads) {
+            const int j = c + tid;
+            const unsigned m = __ballot_sync(0xffffffffu, j >= t && j < T && tokens[j] == id);
+            __syncthreads();                       // previous round's masks have been consumed
+            if (lane == 0) masks[wid] = m;
+            __syncthreads();
+#pragma unroll
+            for (int w = 0; w < kEmbThreads / 32; ++w) {
+                unsigned mm = masks[w];
+                while (mm) {
+                    const int pos = c + w * 32 + __ffs(mm) - 1;
+                    mm &= mm - 1;
+#pragma unroll
+                    for (int k = 0; k < kEmbVec; ++k) {
+                        const int i = i0 + tid + k * kEmbThreads;
+                        if (i < nvec) {
+                            float f[8];
+                            unpack8(ld8(dout + (int64_t)pos * dim + i * 8), f);
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) acc[k][q] += f[q];
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < kEmbVec; ++k) {
+            const int i = i0 + tid + k * kEmbThreads;
+            if (i < nvec) {
+                const bf16x8 o = pack8(acc[k]);
+                st8(dtable + id * dim + i * 8, o);
+                float f[8];
+                unpack8(o, f);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) ss += f[q] * f[q];
+            }
+        }
+    }
+    if (sumsq) {
+        const float total = block_sum(ss, red);
+        if (tid == 0) sumsq[t] = total;
+    }
+}
+
 static inline int grid_for(int64_t work_items, int threads) {
     int64_t blocks = (work_items + threads - 1) / threads;
     const int64_t cap = (int64_t)kNumSMs * 16;
@@ -151,6 +243,18 @@ FTL_API int ftl_embedding_bwd(const int64_t* sorted_tokens, const int64_t* perm,
     if (dim % 8 || ntok <= 0) return (int)cudaErrorInvalidValue;
     embedding_bwd_kernel<<<(unsigned)ntok, 128, 0, stream>>>(sorted_tokens, perm, (const __nv_bfloat16*)dout,
                                                              (__nv_bfloat16*)dtable, ntok, dim, vocab);
+    FTL_LAUNCH_CHECK();
+    return 0;
+}
+
+// Sort-free deterministic embedding backward (see embedding_bwd_direct_kernel).  `prev_tokens` may be null (then the
+// caller guarantees that every row this step does not write is already zero, e.g. after a memset).  sumsq: fp32 [ntok] or null.
+FTL_API int ftl_embedding_bwd_direct(const int64_t* tokens, const int64_t* prev_tokens, const void* dout, void* dtable,
+                                     int64_t ntok, int dim, int vocab, float* sumsq, cudaStream_t stream) {
+    if (dim % 8 || ntok <= 0 || ntok > (1 << 24)) return (int)cudaErrorInvalidValue;
+    const unsigned grid = (unsigned)(prev_tokens ? 2 * ntok : ntok);
+    embedding_bwd_direct_kernel<<<grid, kEmbThreads, 0, stream>>>(tokens, prev_tokens, (const __nv_bfloat16*)dout,
+                                                                  (__nv_bfloat16*)dtable, (int)ntok, dim, vocab, sumsq);
     FTL_LAUNCH_CHECK();
     return 0;
 }

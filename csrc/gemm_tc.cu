@@ -18,20 +18,26 @@
 //               is rounded to bf16 (the Linear's output dtype), adjacent pairs are rotated in fp32 with
 //               the interleaved convention of model.py:121-126, and rounded once more.
 //
-// Structure: persistent, one CTA per SM, 192 threads: warp 0 = TMA producer, warp 1 = TMEM owner + MMA
-// issuer, warps 2-5 = epilogue (warp w may only touch TMEM lanes 32*(w%4)..+31).  4-stage smem ring
-// (48 KB per stage: A 128x64, B 256x64), 2 accumulator stages of 256 TMEM columns each, so the epilogue of
-// tile i overlaps the MMAs of tile i+1.  Tiles are walked M-fastest, so the CTAs running at the same time
-// share a B (weight) tile through L2 and the weight matrix streams from HBM exactly once.
+//   EPI_SWIGLU_BWD  the w2 dgrad GEMM (dact = dx @ w2) whose epilogue reads the saved gate / up tiles and writes
+//               dgate = dact * up * silu'(gate) and dup = dact * silu(gate): dact never exists in memory.
+//   sumsq       any plain GEMM can also return per-(CTA, epilogue warp) sums of squares of the bf16 values it stored:
+//               the weight-gradient GEMMs produce the global gradient norm's partials as they write the gradient.
+//
+// Two kernels share the epilogues.  Default (gemm_tc2_kernel): persistent CTA pairs, tcgen05 cta_group::2 — the two
+// SMs of a TPC compute one 256 x 256 tile, each CTA stages its 128 rows of A and half of the B tile (6-stage, 32 KB
+// per stage TMA ring), the leader issues M=256 UMMAs, two accumulator stages of 256 TMEM columns let the epilogue of
+// tile i overlap the MMAs of tile i+1; warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2-5 = epilogue
+// (and, in the FSDP variants, the NVLink gather of the weight operand).  gemm_tc_kernel (FTL_GEMM_CLUSTER=1/2/4) is
+// the earlier single-CTA-MMA kernel with a 4-stage ring and optional cluster multicast of B; kept as a baseline.
+// Tiles are walked M-fastest, so CTAs running at the same time share a B (weight) tile through L2.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cudaTypedefs.h>
 
 #include <stdlib.h>
 
-#include <mutex>
-
 #include "common/ptx.cuh"
+#include "common/tmap_cache.cuh"
 #include "common/util.cuh"
 
 namespace ftl {
@@ -41,7 +47,7 @@ constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kAByte
 constexpr int kGemmThreads = 192;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 
-enum { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_ROPE = 2 };
+enum { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_ROPE = 2, EPI_SWIGLU_BWD = 3 };
 
 struct GemmArgs {
     __nv_bfloat16* C;       // PLAIN/ROPE: [M, N]; SWIGLU: act [M, N/2]
@@ -49,6 +55,10 @@ struct GemmArgs {
     __nv_bfloat16* C_up;
     const float* cos_t;     // ROPE: fp32 [seq_len, head_dim/2]
     const float* sin_t;
+    __nv_bfloat16* C2;      // SWIGLU_BWD: dup (C = dgate)
+    const __nv_bfloat16* in_gate;   // SWIGLU_BWD: saved pre-activations [M, N] (ldc)
+    const __nv_bfloat16* in_up;
+    float* sumsq;           // optional [gridDim.x * 4]: sum of squares of the bf16 outputs per (CTA, epilogue warp)
     int64_t ldc;
     int M, N, K;            // N counts accumulator columns (SWIGLU: 2 x hidden)
     int nk1;                // k-blocks served by the first (A, B) pair; the rest come from the second
@@ -145,8 +155,51 @@ __device__ __forceinline__ bool wide_ok(const void* p, int64_t ld) {
 }
 
 template <int kEpi>
-__device__ __forceinline__ void epilogue_tile(const GemmArgs& g, uint32_t taddr, int row, int n_blk) {
-                if (kEpi == EPI_SWIGLU) {
+__device__ __forceinline__ void epilogue_tile(const GemmArgs& g, uint32_t taddr, int row, int n_blk, float& ss) {
+                if (kEpi == EPI_SWIGLU_BWD) {
+                    // accumulator = dact tile.  N % 16 == 0, ldc % 16 == 0 and 32-byte aligned bases (checked on the
+                    // host): every 16-column group is read and written with 32-byte row accesses.
+                    const int n0 = n_blk * BN;
+    #pragma unroll 1
+                    for (int c = 0; c < BN; c += 32) {
+                        uint32_t gw[2][8], uw[2][8];
+                        const bool live = row < g.M;
+                        const int64_t off0 = (int64_t)row * g.ldc + n0 + c;
+                        bool in[2];
+    #pragma unroll
+                        for (int h = 0; h < 2; ++h) {        // issue the gate / up loads before waiting on TMEM
+                            in[h] = live && (n0 + c + h * 16 < g.N);
+                            if (in[h]) {
+                                ld_row32(g.in_gate + off0 + h * 16, gw[h]);
+                                ld_row32(g.in_up + off0 + h * 16, uw[h]);
+                            }
+                        }
+                        uint32_t r[32];
+                        ptx::tmem_ld32(taddr + c, r);
+                        ptx::tmem_ld_wait();
+    #pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            if (!in[h]) continue;
+                            bf16x8 og[2], ou[2];
+    #pragma unroll
+                            for (int v = 0; v < 2; ++v) {
+                                float gt[8], up[8], a[8], b[8];
+                                unpack8(*reinterpret_cast<const bf16x8*>(&gw[h][v * 4]), gt);
+                                unpack8(*reinterpret_cast<const bf16x8*>(&uw[h][v * 4]), up);
+    #pragma unroll
+                                for (int j = 0; j < 8; ++j) {
+                                    const float d = round_bf16(__uint_as_float(r[h * 16 + v * 8 + j]));   // dact in bf16, as autograd
+                                    const float sig = 1.f / (1.f + __expf(-gt[j]));
+                                    a[j] = d * up[j] * (sig * (1.f + gt[j] * (1.f - sig)));
+                                    b[j] = d * (gt[j] * sig);
+                                }
+                                og[v] = pack8(a); ou[v] = pack8(b);
+                            }
+                            st_row32(g.C + off0 + h * 16, og[0], og[1]);
+                            st_row32(g.C2 + off0 + h * 16, ou[0], ou[1]);
+                        }
+                    }
+                } else if (kEpi == EPI_SWIGLU) {
                     const int h0 = n_blk * (BN / 2);   // first hidden column of this tile
                     const int hidden = g.N / 2;
                     const bool w_act = wide_ok(g.C, g.ldc), w_gate = wide_ok(g.C_gate, g.ldc), w_up = wide_ok(g.C_up, g.ldc);
@@ -206,6 +259,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmArgs& g, uint32_t taddr,
                                     }
                                 }
                                 o[v] = pack8(f);
+                                if (kEpi == EPI_PLAIN && g.sumsq != nullptr && col < g.N) {   // norm² of what is stored
+                                    float q[8];
+                                    unpack8(o[v], q);
+    #pragma unroll
+                                    for (int j = 0; j < 8; ++j) ss += q[j] * q[j];
+                                }
                             }
                             store_groups(g.C, w_c, (int64_t)row * g.ldc + n0 + c, o, n0 + c, g.N);
                         }
@@ -358,6 +417,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int q = warp & 3;                 // TMEM lane quarter this warp may read
         int acc = 0;
         uint32_t acc_phase = 0;
+        float ss = 0.f;
         for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
             const int m0 = ((unit % m_groups) * kCluster + crank) * BM;
             const int n_blk = unit / m_groups;
@@ -365,12 +425,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             ptx::mbar_wait(&acc_full[acc], acc_phase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
-            epilogue_tile<kEpi>(g, taddr, row, n_blk);
+            epilogue_tile<kEpi>(g, taddr, row, n_blk, ss);
             // every TMEM read of this accumulator stage has completed (wait::ld above): hand it back
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&acc_empty[acc]);
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (g.sumsq != nullptr) {               // fixed tile -> CTA map and fixed shuffle tree: deterministic
+            ss = warp_sum(ss);
+            if (lane == 0) g.sumsq[blockIdx.x * 4 + q] = ss;
         }
     }
     ptx::tc_fence_before();
@@ -528,6 +592,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         int acc = 0;
         uint32_t acc_phase = 0;
         bool gather_left = g.gather_src != nullptr;
+        float ss = 0.f;
         for (int unit = pair_id; unit < num_units; unit += num_pairs) {
             const int m0 = ((unit % m_pairs) * 2 + crank) * BM;
             const int n_blk = (unit / m_pairs + n_rot) % n_tiles;
@@ -537,11 +602,15 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             ptx::mbar_wait(&acc_full[acc], acc_phase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
-            epilogue_tile<kEpi>(g, taddr, row, n_blk);
+            epilogue_tile<kEpi>(g, taddr, row, n_blk, ss);
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&acc_empty[acc]), 0));
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (g.sumsq != nullptr) {
+            ss = warp_sum(ss);
+            if (lane == 0) g.sumsq[blockIdx.x * 4 + q] = ss;
         }
         while (gather_left) gather_left = gather_one_item(g, lane);   // CTAs without tiles still help
     }
@@ -552,30 +621,11 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 }
 
 // ------------------------------------------------------------------------------------------------ host
-static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
-static std::once_flag g_encode_once;
-
-static void load_encode() {
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-        g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
-}
-
 // Row-major bf16 matrix [rows, cols] (leading dimension ld elements); box = {box_cols (contiguous), box_rows}.
+// Encoded once per (pointer, shape, box) and cached (common/tmap_cache.cuh).
 static int make_tmap(CUtensorMap* out, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_cols,
                      int box_rows) {
-    std::call_once(g_encode_once, load_encode);
-    if (!g_encode) return (int)cudaErrorNotSupported;
-    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+    return g_tmaps.get(out, ptr, rows, cols, ld, box_cols, box_rows);
 }
 
 template <int kEpi, bool kAMn, bool kBMn, int kCluster>
@@ -689,9 +739,13 @@ using namespace ftl;
 //   a_mn = 0: a is [M, K] (lda);  a_mn = 1: a is [K, M] (lda)  — i.e. C = a^T ...
 //   b_mn = 0: b is [N, K] (ldb);  b_mn = 1: b is [K, N] (ldb)
 // Optional second reduction segment (a2, b2, K2): C = A·B + A2·B2.  max_ctas = 0 uses all 148 SMs.
-FTL_API int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c,
-                          int64_t ldc, int M, int N, int K, const void* a2, int64_t lda2, const void* b2, int64_t ldb2,
-                          int K2, int max_ctas, cudaStream_t stream) {
+// sumsq (optional): fp32 [ftl_gemm_sumsq_slots()] receiving the per-(CTA, epilogue warp) sums of squares of the stored
+// bf16 values; entries past the launched grid are left untouched (keep them zero).
+FTL_API int ftl_gemm_sumsq_slots(void) { return kNumSMs * 4; }
+
+FTL_API int ftl_gemm_bf16_ex(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c,
+                             int64_t ldc, int M, int N, int K, const void* a2, int64_t lda2, const void* b2, int64_t ldb2,
+                             int K2, float* sumsq, int max_ctas, cudaStream_t stream) {
     if (M <= 0 || N <= 0 || K <= 0 || (N % 8) || (ldc % 8) || (lda % 8) || (ldb % 8) || (K % BK && K2 > 0))
         return (int)cudaErrorInvalidValue;
     CUtensorMap ta, tb, ta2, tb2;
@@ -715,10 +769,39 @@ FTL_API int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, i
     g.ldc = ldc;
     g.M = M; g.N = N; g.K = K + (K2 > 0 ? K2 : 0);
     g.nk1 = (K + BK - 1) / BK;
+    g.sumsq = sumsq;
     if (!a_mn && !b_mn) return launch<EPI_PLAIN, false, false>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
     if (!a_mn && b_mn) return launch<EPI_PLAIN, false, true>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
     if (a_mn && b_mn) return launch<EPI_PLAIN, true, true>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
     return launch<EPI_PLAIN, true, false>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
+}
+
+FTL_API int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c,
+                          int64_t ldc, int M, int N, int K, const void* a2, int64_t lda2, const void* b2, int64_t ldb2,
+                          int K2, int max_ctas, cudaStream_t stream) {
+    return ftl_gemm_bf16_ex(a, lda, a_mn, b, ldb, b_mn, c, ldc, M, N, K, a2, lda2, b2, ldb2, K2, nullptr, max_ctas, stream);
+}
+
+// SwiGLU backward fused into the w2 dgrad GEMM: dact = dx [M, K] @ w2 [K, H] stays in TMEM; the epilogue reads the saved
+// gate / up [M, H] and writes dgate, dup [M, H] (all four with leading dimension ldo).  H and ldo multiples of 16,
+// 32-byte aligned bases.  Replaces a [M, H] bf16 round trip and one elementwise kernel (reference: autograd of
+// model.py:254).
+FTL_API int ftl_gemm_swiglu_bwd(const void* dx, int64_t lddx, const void* w2, int64_t ldw, const void* gate, const void* up,
+                                void* dgate, void* dup, int64_t ldo, int M, int H, int K, int max_ctas, cudaStream_t stream) {
+    auto al32 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; };
+    if (M <= 0 || H <= 0 || K <= 0 || (H % 16) || (ldo % 16) || (lddx % 8) || (ldw % 8) || !al32(gate) || !al32(up) ||
+        !al32(dgate) || !al32(dup))
+        return (int)cudaErrorInvalidValue;
+    CUtensorMap ta, tb;
+    int e;
+    if ((e = make_tmap(&ta, dx, M, K, lddx, BK, BM))) return e;
+    if ((e = make_tmap(&tb, w2, K, H, ldw, 64, BK))) return e;     // MN-major B: boxes {64 n, 64 r}
+    GemmArgs g{};
+    g.C = (__nv_bfloat16*)dgate; g.C2 = (__nv_bfloat16*)dup;
+    g.in_gate = (const __nv_bfloat16*)gate; g.in_up = (const __nv_bfloat16*)up;
+    g.ldc = ldo;
+    g.M = M; g.N = H; g.K = K; g.nk1 = (K + BK - 1) / BK;
+    return launch<EPI_SWIGLU_BWD, false, true>(gemm_cluster(w2, nullptr), ta, tb, ta, tb, g, max_ctas, stream);
 }
 
 // gate|up dual GEMM with the SwiGLU epilogue: x [M, K], w1 / w3 [H, K]; writes act (and gate, up if non-null), [M, H].

@@ -153,8 +153,10 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
 
 // Fold the per-CTA partial rows: block = 32 columns x 8 row lanes; lane py adds partials py, py+8, ... in order,
 // the 8 lanes are then added in fixed order through shared memory (deterministic).  Reads are 128-byte coalesced.
+// sumsq (optional, one float per block): sum of squares of the 32 bf16 values this block stored (gradient-norm partial).
 __global__ void __launch_bounds__(256)
-rmsnorm_dw_finalize_kernel(const float* __restrict__ partial, int nparts, int dim, __nv_bfloat16* __restrict__ dw) {
+rmsnorm_dw_finalize_kernel(const float* __restrict__ partial, int nparts, int dim, __nv_bfloat16* __restrict__ dw,
+                           float* __restrict__ sumsq = nullptr) {
     __shared__ float acc[8][33];
     const int cx = threadIdx.x & 31, py = threadIdx.x >> 5;
     const int j = blockIdx.x * 32 + cx;
@@ -163,11 +165,20 @@ rmsnorm_dw_finalize_kernel(const float* __restrict__ partial, int nparts, int di
         for (int p = py; p < nparts; p += 8) s += partial[(int64_t)p * dim + j];
     acc[py][cx] = s;
     __syncthreads();
-    if (py == 0 && j < dim) {
-        float t = 0.f;
+    if (py == 0) {
+        float sq = 0.f;
+        if (j < dim) {
+            float t = 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) t += acc[k][cx];
-        dw[j] = __float2bfloat16_rn(t);
+            for (int k = 0; k < 8; ++k) t += acc[k][cx];
+            const __nv_bfloat16 o = __float2bfloat16_rn(t);
+            dw[j] = o;
+            sq = __bfloat162float(o) * __bfloat162float(o);
+        }
+        if (sumsq) {
+            sq = warp_sum(sq);
+            if (cx == 0) sumsq[blockIdx.x] = sq;
+        }
     }
 }
 
@@ -210,6 +221,25 @@ FTL_API int ftl_rmsnorm_fwd(const void* x, const void* delta, void* h_out, const
     auto W = (const __nv_bfloat16*)w; auto Y = (__nv_bfloat16*)y;
     if (delta) rmsnorm_fwd_kernel<true><<<rows, threads, 0, stream>>>(X, D, H, W, Y, rstd, dim, eps);
     else rmsnorm_fwd_kernel<false><<<rows, threads, 0, stream>>>(X, nullptr, nullptr, W, Y, rstd, dim, eps);
+    FTL_LAUNCH_CHECK();
+    return 0;
+}
+
+FTL_API int ftl_rmsnorm_sumsq_slots(int dim) { return (dim + 31) / 32; }
+
+// scratch: fp32 [ftl_rmsnorm_partials(rows), dim];  sumsq: optional fp32 [ftl_rmsnorm_sumsq_slots(dim)] receiving the
+// sum of squares of the stored d(weight), in pieces
+FTL_API int ftl_rmsnorm_bwd_ex(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                               void* dx, void* dw, float* scratch, float* sumsq, int rows, int dim, cudaStream_t stream) {
+    if (dim % 8 || dim > 8 * kNormMaxVec * 256 || rows <= 0) return (int)cudaErrorInvalidValue;
+    int threads = norm_threads(dim);
+    if (threads > 256) threads = 256;
+    const int parts = ftl_rmsnorm_partials(rows);
+    auto DY = (const __nv_bfloat16*)dy; auto X = (const __nv_bfloat16*)x; auto W = (const __nv_bfloat16*)w;
+    auto DR = (const __nv_bfloat16*)dres; auto DX = (__nv_bfloat16*)dx;
+    launch_rmsnorm_bwd(parts, threads, stream, DY, X, W, rstd, DR, DX, scratch, rows, dim);
+    FTL_LAUNCH_CHECK();
+    rmsnorm_dw_finalize_kernel<<<(dim + 31) / 32, 256, 0, stream>>>(scratch, parts, dim, (__nv_bfloat16*)dw, sumsq);
     FTL_LAUNCH_CHECK();
     return 0;
 }

@@ -12,8 +12,10 @@ step is a fixed launch sequence over preallocated buffers:
   * activations are saved in static per-layer buffers (8.7 GB at seq 2048 — 180 GB of HBM makes
     recomputation pointless here), which also makes the step CUDA-graph capturable.
 
-Plain GEMMs go through cuBLAS (`torch.mm(out=)`) unless the tcgen05 kernels of csrc/gemm_*.cu are
-enabled for that shape; attention uses the library SDPA until csrc/attn_*.cu covers it.
+Every GEMM of the step is the hand-written tcgen05 CTA-pair kernel of csrc/gemm_tc.cu (RoPE, SwiGLU forward and
+SwiGLU backward in its epilogues, gradient-norm partials out of the weight-gradient epilogues); attention is the
+tcgen05 flash kernel of csrc/attn_tc.cu (deterministic forward and backward).  `FTL_GEMM=cublas` / `FTL_ATTN=lib`
+switch either back to the library op for A/B comparisons.
 """
 from __future__ import annotations
 
@@ -208,7 +210,9 @@ class NativeEngine:
         self.dx_a, self.dx_b = bf(T, d), bf(T, d)
         self.dh = bf(T, d)
         self.dtmp = bf(T, d)
-        self.dact = bf(T, Fh)
+        # SwiGLU backward rides in the epilogue of the w2 dgrad GEMM (no dact buffer) when the 32-byte row accesses fit
+        self.fused_swiglu_bwd = self.USE_TC and Fh % 16 == 0
+        self.dact = None if self.fused_swiglu_bwd else bf(T, Fh)
         self.dgate, self.dup = bf(T, Fh), bf(T, Fh)
         self.dqkv = bf(T, self.qkv_dim)
         self.dattn = bf(T, H * hd)
@@ -238,9 +242,38 @@ class NativeEngine:
         self.hook_params = None
         self.hook_grads = None
         self.sparse_emb_zero, self._emb_dirty = False, None   # see backward(): set by single-rank trainers
+        # Gradient-norm partials produced by the kernels that write the gradients (single-rank pipelined trainer): one
+        # slice per producing launch, handed out in launch order, summed in index order by the publish kernel.
+        self.norm_arena: Optional[torch.Tensor] = None
+        self._arena_off = 0
         self.hook_params_bwd = None   # called before the backward of bucket b reads its parameters
         self.fused_gather = None      # FSDP: object with qkv(i, x, out) / swiglu(i, x, act, gate, up) running the
                                       # gather-fused GEMMs for layer i (parallel/fsdp.py)
+
+    def enable_fused_norm(self) -> bool:
+        """Allocate the arena for sum-of-squares partials written by the weight-gradient GEMMs, the norm-weight
+        finalize kernels and the embedding backward.  Replaces a 16 GB re-read of the gradient buffer per step."""
+        if not self.USE_TC:
+            return False
+        c = self.cfg
+        gs, ns = N.gemm_sumsq_slots(), N.rmsnorm_sumsq_slots(c.dim)
+        n = c.n_layers * (5 * gs + 2 * ns) + gs + ns + self.T
+        self.norm_arena = torch.zeros(n, dtype=torch.float32, device=self.dev)
+        return True
+
+    def _sq(self, n: int) -> Optional[torch.Tensor]:
+        if self.norm_arena is None:
+            return None
+        o = self._arena_off
+        self._arena_off = o + n
+        assert self._arena_off <= self.norm_arena.numel()
+        return self.norm_arena[o:o + n]
+
+    def _sq_gemm(self):
+        return self._sq(N.gemm_sumsq_slots()) if self.norm_arena is not None else None
+
+    def _sq_norm(self):
+        return self._sq(N.rmsnorm_sumsq_slots(self.cfg.dim)) if self.norm_arena is not None else None
 
     def _need(self, upto: int) -> None:
         if self.hook_params is not None:
@@ -272,8 +305,9 @@ class NativeEngine:
         return out
 
     def gemm_tn(self, a, b, out):
+        """Weight gradient out = a^T @ b; also the producer of its share of the gradient-norm partials."""
         if self.USE_TC:
-            return N.gemm(a, b, out, a_mn=True, b_mn=True)
+            return N.gemm(a, b, out, a_mn=True, b_mn=True, sumsq=self._sq_gemm())
         return torch.mm(a.t(), b, out=out)
 
     # ---- attention (library SDPA island; replaced by csrc/attn when available) -------------------
@@ -359,12 +393,13 @@ class NativeEngine:
         rot = (H + KV) * hd
         L = c.n_layers
         dl = self.logits
+        self._arena_off = 0
         if self.hook_params_bwd is not None:
             self.hook_params_bwd(L + 1)
         self.gemm_tn(dl, self.xf, self.g_out)                     # dW_out
         self.gemm_nn(dl, self.w_out, self.dtmp)                   # d xf
         dx, spare = self.dx_a, self.dx_b
-        N.rmsnorm_bwd(self.dtmp, self.x[L], self.w_fn, self.rstd_f, dx, self.g_fn, self.norm_scratch)
+        N.rmsnorm_bwd(self.dtmp, self.x[L], self.w_fn, self.rstd_f, dx, self.g_fn, self.norm_scratch, sumsq=self._sq_norm())
         if self.hook_grads is not None:
             self.hook_grads(L + 1)
         for i in range(L - 1, -1, -1):
@@ -373,14 +408,17 @@ class NativeEngine:
                 self.hook_params_bwd(i + 1)
             # x_{i+1} = h + w2(act)
             self.gemm_tn(dx, self.act[i], lw["gw2"])
-            self.gemm_nn(dx, lw["ww2"], self.dact)
-            N.swiglu_bwd(self.dact, self.gate[i], self.up[i], self.dgate, self.dup)
+            if self.fused_swiglu_bwd:   # d act -> (d gate, d up) in the dgrad epilogue
+                N.gemm_swiglu_bwd(dx, lw["ww2"], self.gate[i], self.up[i], self.dgate, self.dup)
+            else:
+                self.gemm_nn(dx, lw["ww2"], self.dact)
+                N.swiglu_bwd(self.dact, self.gate[i], self.up[i], self.dgate, self.dup)
             self.gemm_tn(self.dgate, self.hn[i], lw["gw1"])
             self.gemm_tn(self.dup, self.hn[i], lw["gw3"])
             self.gemm_nn(self.dgate, lw["ww1"], self.dtmp, a2=self.dup, b2=lw["ww3"])   # one pass over K = 2F
             # dh = dx + d ffn_norm
             N.rmsnorm_bwd(self.dtmp, self.h[i], lw["wfn"], self.rstd2[i], self.dh, lw["gfn"], self.norm_scratch,
-                          dres=dx)
+                          dres=dx, sumsq=self._sq_norm())
             # h = x + wo(attn)
             a = self.attn_o[i] if self.own_attn else self.attn[i].transpose(1, 2).reshape(T, H * hd)
             self.gemm_tn(self.dh, a, lw["go"])
@@ -391,24 +429,25 @@ class NativeEngine:
             self.gemm_tn(self.dqkv, self.xn[i], lw["gqkv"])
             self.gemm_nn(self.dqkv, lw["wqkv"], self.dtmp)
             N.rmsnorm_bwd(self.dtmp, self.x[i], lw["wan"], self.rstd1[i], spare, lw["gan"], self.norm_scratch,
-                          dres=self.dh)
+                          dres=self.dh, sumsq=self._sq_norm())
             dx, spare = spare, dx
             if self.hook_grads is not None:
                 self.hook_grads(i + 1)
-        # embedding: deterministic scatter-add into a zero table gradient.  The table gradient is 1 GB and only the rows
-        # of this batch's tokens are written, so when nobody else writes into it (single rank: no in-place reduction
-        # of peers' rows) only the rows the PREVIOUS step touched are cleared instead of the whole buffer.
+        # embedding: deterministic scatter-add into a zero table gradient, without a sort (csrc/elementwise.cu).  The
+        # table gradient is 1 GB and only the rows of this batch's tokens are written, so when nobody else writes into
+        # it (single rank: no in-place reduction of peers' rows) the kernel itself clears the rows the PREVIOUS step
+        # touched and this one does not, instead of a memset of the whole buffer.
         flat_tok = tokens.view(-1)
+        prev = None
         if self.sparse_emb_zero and self._emb_dirty is not None:
-            self.g_emb.index_fill_(0, self._emb_dirty, 0)
+            prev = self._emb_dirty
         else:
             self.g_emb.zero_()
+        N.embedding_bwd_direct(flat_tok, prev, dx, self.g_emb, sumsq=self._sq(self.T))
         if self.sparse_emb_zero:
             if self._emb_dirty is None:
                 self._emb_dirty = torch.empty_like(flat_tok)
-            self._emb_dirty.copy_(flat_tok.clamp(0, self.cfg.vocab_size - 1))   # ids the kernels skip must not index
-        sorted_tok, perm = torch.sort(flat_tok, stable=True)
-        N.embedding_bwd(sorted_tok, perm, dx, self.g_emb)
+            self._emb_dirty.copy_(flat_tok)   # device-to-device copy; the kernel ignores ids outside the table
         if self.hook_grads is not None:
             self.hook_grads(0)
 

@@ -85,6 +85,12 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_attn_fwd", [P, I64, P, I64, P, I, I, I, I, I, P])
     _sig(L, "ftl_attn_bwd", [P, I64, P, P, I64, P, P, P, P, P, P, I, I, I, I, I, P])
     _sig(L, "ftl_attn_bwd_scratch_bytes", [I, I, I, I, I], c_int64)
+    _sig(L, "ftl_gemm_sumsq_slots", [])
+    _sig(L, "ftl_gemm_bf16_ex", [P, I64, I, P, I64, I, P, I64, I, I, I, P, I64, P, I64, I, P, I, P])
+    _sig(L, "ftl_gemm_swiglu_bwd", [P, I64, P, I64, P, P, P, P, I64, I, I, I, I, P])
+    _sig(L, "ftl_rmsnorm_sumsq_slots", [I])
+    _sig(L, "ftl_rmsnorm_bwd_ex", [P, P, P, P, P, P, P, P, P, I, I, P])
+    _sig(L, "ftl_embedding_bwd_direct", [P, P, P, P, I64, I, I, P, P])
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -136,12 +142,18 @@ def rmsnorm_partials(rows: int) -> int:
     return lib().ftl_rmsnorm_partials(rows)
 
 
-def rmsnorm_bwd(dy, x, w, rstd, dx, dw, scratch, dres=None):
+def rmsnorm_sumsq_slots(dim: int) -> int:
+    return lib().ftl_rmsnorm_sumsq_slots(dim)
+
+
+def rmsnorm_bwd(dy, x, w, rstd, dx, dw, scratch, dres=None, sumsq=None):
+    """sumsq: optional fp32 [rmsnorm_sumsq_slots(dim)] receiving the pieces of sum(dw^2) (gradient-norm partials)."""
     _bf16(dy, x, w, dx, dw, dres)
     rows, dim = x.shape
     assert scratch.dtype == torch.float32 and scratch.numel() >= rmsnorm_partials(rows) * dim
-    _check(lib().ftl_rmsnorm_bwd(_ptr(dy), _ptr(x), _ptr(w), _ptr(rstd), _ptr(dres), _ptr(dx), _ptr(dw),
-                                 _ptr(scratch), rows, dim, _stream()), "ftl_rmsnorm_bwd", 2)
+    assert sumsq is None or (sumsq.dtype == torch.float32 and sumsq.numel() >= rmsnorm_sumsq_slots(dim))
+    _check(lib().ftl_rmsnorm_bwd_ex(_ptr(dy), _ptr(x), _ptr(w), _ptr(rstd), _ptr(dres), _ptr(dx), _ptr(dw),
+                                    _ptr(scratch), _ptr(sumsq), rows, dim, _stream()), "ftl_rmsnorm_bwd", 2)
     return dx
 
 
@@ -180,6 +192,18 @@ def embedding_bwd(sorted_tokens, perm, dout, dtable):
                                    dtable.shape[1], dtable.shape[0], _stream()), "ftl_embedding_bwd")
 
 
+def embedding_bwd_direct(tokens, prev_tokens, dout, dtable, sumsq=None):
+    """Sort-free deterministic scatter-add of dout rows into the table gradient.  prev_tokens (or None): ids whose rows
+    the previous step wrote; those not written by this step are cleared.  Rows outside both sets must already be zero."""
+    _bf16(dout, dtable)
+    assert tokens.dtype == torch.int64 and tokens.is_contiguous()
+    assert prev_tokens is None or (prev_tokens.dtype == torch.int64 and prev_tokens.numel() == tokens.numel())
+    assert sumsq is None or (sumsq.dtype == torch.float32 and sumsq.numel() >= tokens.numel())
+    _check(lib().ftl_embedding_bwd_direct(_ptr(tokens), _ptr(prev_tokens), _ptr(dout), _ptr(dtable), tokens.numel(),
+                                          dtable.shape[1], dtable.shape[0], _ptr(sumsq), _stream()),
+           "ftl_embedding_bwd_direct")
+
+
 def cross_entropy(logits, labels, inv_n, row_loss, loss_out, row_lse=None, write_grad=True):
     """In place: logits [rows, V] bf16 become d(loss)/d(logits).  loss_out[0] = sum(CE) * inv_n."""
     assert logits.dtype == torch.bfloat16 and logits.stride(1) == 1 and labels.dtype == torch.int64
@@ -211,12 +235,18 @@ def _mat(t):
     return t
 
 
-def gemm(a, b, out, a_mn=False, b_mn=False, a2=None, b2=None, max_ctas=0):
+def gemm_sumsq_slots() -> int:
+    return lib().ftl_gemm_sumsq_slots()
+
+
+def gemm(a, b, out, a_mn=False, b_mn=False, a2=None, b2=None, max_ctas=0, sumsq=None):
     """out[M, N] = A . B^T-style product on the tcgen05 path.
 
     a_mn=False: a is [M, K];  a_mn=True: a is [K, M] (A = a^T).
     b_mn=False: b is [N, K];  b_mn=True: b is [K, N].
-    Optional second reduction segment (a2, b2) is added: out = A.B + A2.B2."""
+    Optional second reduction segment (a2, b2) is added: out = A.B + A2.B2.
+    sumsq: optional fp32 [gemm_sumsq_slots()]; receives partial sums of squares of the stored bf16 values (their
+    total is sum(out^2); entries the launch does not use are left as they are — keep them zero)."""
     _mat(a), _mat(b), _mat(out)
     M, N = out.shape
     K = a.shape[0] if a_mn else a.shape[1]
@@ -226,10 +256,23 @@ def gemm(a, b, out, a_mn=False, b_mn=False, a2=None, b2=None, max_ctas=0):
     if a2 is not None:
         _mat(a2), _mat(b2)
         K2 = a2.shape[0] if a_mn else a2.shape[1]
-    _check(lib().ftl_gemm_bf16(_ptr(a), a.stride(0), int(a_mn), _ptr(b), b.stride(0), int(b_mn), _ptr(out),
-                               out.stride(0), M, N, K, _ptr(a2), a2.stride(0) if a2 is not None else 0, _ptr(b2),
-                               b2.stride(0) if b2 is not None else 0, K2, max_ctas, _stream()), "ftl_gemm_bf16")
+    assert sumsq is None or (sumsq.dtype == torch.float32 and sumsq.numel() >= gemm_sumsq_slots())
+    _check(lib().ftl_gemm_bf16_ex(_ptr(a), a.stride(0), int(a_mn), _ptr(b), b.stride(0), int(b_mn), _ptr(out),
+                                  out.stride(0), M, N, K, _ptr(a2), a2.stride(0) if a2 is not None else 0, _ptr(b2),
+                                  b2.stride(0) if b2 is not None else 0, K2, _ptr(sumsq), max_ctas, _stream()),
+           "ftl_gemm_bf16")
     return out
+
+
+def gemm_swiglu_bwd(dx, w2, gate, up, dgate, dup, max_ctas=0):
+    """dgate, dup = SwiGLU backward of dact = dx @ w2, computed in the GEMM epilogue (dact is never stored).
+    dx [M, K]; w2 [K, H] (the Linear's [out, in] weight); gate / up / dgate / dup [M, H], H % 16 == 0."""
+    _mat(dx), _mat(w2), _mat(gate), _mat(up), _mat(dgate), _mat(dup)
+    M, K = dx.shape
+    H = w2.shape[1]
+    assert w2.shape[0] == K and gate.shape == (M, H) and gate.stride(0) == up.stride(0) == dgate.stride(0) == dup.stride(0)
+    _check(lib().ftl_gemm_swiglu_bwd(_ptr(dx), dx.stride(0), _ptr(w2), w2.stride(0), _ptr(gate), _ptr(up), _ptr(dgate),
+                                     _ptr(dup), gate.stride(0), M, H, K, max_ctas, _stream()), "ftl_gemm_swiglu_bwd")
 
 
 def gemm_swiglu(x, w1, w3, act, gate=None, up=None, max_ctas=0):

@@ -96,6 +96,10 @@ class PipelinedTrainer(NativeTrainer):
         if fresh:
             self.engine.hook_params = self._wait_params
             self.engine.hook_grads = self._grads_done
+            # One rank has nothing to reduce: the kernels that write the gradients also emit the norm partials, and
+            # phase 1 (a 16 GB re-read of the gradient buffer at W = 1) disappears.
+            self.fused_norm = (type(self) is PipelinedTrainer and self.env.world_size == 1
+                               and os.environ.get("FTL_FUSED_NORM", "1") != "0" and self.engine.enable_fused_norm())
 
     def _wait_params(self, b: int) -> None:
         """Forward is about to read bucket b: wait until last step's update of it has landed everywhere."""
@@ -113,6 +117,8 @@ class PipelinedTrainer(NativeTrainer):
         self.ev_grad[b].record()
         with torch.cuda.stream(self.comm):
             self.comm.wait_event(self.ev_grad[b])
+            if getattr(self, "fused_norm", False):
+                return
             self._barrier()          # every rank's bucket-b gradients are complete
             for (a, e), k in zip(self.ranges[b], self.range_slot[b]):
                 part = self.rs_partials[k * self.parts:(k + 1) * self.parts]
@@ -129,7 +135,8 @@ class PipelinedTrainer(NativeTrainer):
     def _reduce_and_update(self, hyper: torch.Tensor, loss: torch.Tensor) -> None:
         env, f, W = self.env, self.flat, self.env.world_size
         with torch.cuda.stream(self.comm):
-            N.dp_publish(self.rs_partials, self.rs_partials.numel(), loss, self.symm.table("slots"), env.rank, W)
+            parts = self.engine.norm_arena if getattr(self, "fused_norm", False) else self.rs_partials
+            N.dp_publish(parts, parts.numel(), loss, self.symm.table("slots"), env.rank, W)
             self._barrier()          # all slots written; nobody still reads my gradients for phase 1
             N.dp_finalize(self.slots, W, hyper, self.stats, loss, clip=(self.clip_mode == "clip"))
             self._result_handle = self._publish_result_on_comm(loss)

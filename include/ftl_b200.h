@@ -27,6 +27,11 @@ int ftl_rmsnorm_partials(int rows);
 /* dx = d(norm)/dx (+ dres if not NULL, the residual-path gradient); dw = bf16 weight gradient. */
 int ftl_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
                     void* dx, void* dw, float* scratch, int rows, int dim, ftl_stream_t stream);
+/* Same, and sumsq (fp32 [ftl_rmsnorm_sumsq_slots(dim)], may be NULL) receives sum(dw^2) in pieces: the gradient-norm
+ * partial of this weight, produced where the gradient is written (reference: utils.py:58-63 re-reads every gradient). */
+int ftl_rmsnorm_sumsq_slots(int dim);
+int ftl_rmsnorm_bwd_ex(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                       void* dx, void* dw, float* scratch, float* sumsq, int rows, int dim, ftl_stream_t stream);
 
 /* Same backward, for callers that cannot supply scratch (no counterpart in the reference, which has no
  * native code and lets PyTorch allocate).  Meant for the recovery path after a CUDA out-of-memory error and
@@ -34,7 +39,9 @@ int ftl_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* r
  * fails, so the work area is a 4 849 664-byte array inside the library image (held by each GPU that loads
  * the library until exit).  Limit: dim <= 4096; larger requests return cudaErrorInvalidValue and set
  * ftl_last_error().  Allocates nothing.  The first call on each device resolves the array's device address
- * (do it outside stream capture).  Calls share the array: calls that may overlap on one GPU race. */
+ * (do it outside stream capture) and stores it in a per-device table without taking a lock: two host threads
+ * that make their first call on the same device at the same moment both store the same value, which is harmless.
+ * Calls share the array: calls that may overlap on one GPU race. */
 int ftl_rmsnorm_bwd_static(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
                            void* dx, void* dw, int rows, int dim, ftl_stream_t stream);
 int64_t ftl_rmsnorm_bwd_static_capacity(void);   /* bytes of the built-in work area */
@@ -55,6 +62,11 @@ int ftl_embedding_fwd(const int64_t* tokens, const void* table, void* out, int64
 /* deterministic: sorted_tokens/perm = stable ascending sort of the token ids; dtable must be zero */
 int ftl_embedding_bwd(const int64_t* sorted_tokens, const int64_t* perm, const void* dout, void* dtable,
                       int64_t ntok, int dim, int vocab, ftl_stream_t stream);
+/* deterministic and sort-free: the CTA of the first position holding an id sums that id's dout rows in position order.
+ * prev_tokens (may be NULL): ids whose rows the previous call wrote; rows this call does not write are cleared, so the
+ * 1 GB table gradient never needs a memset.  sumsq (fp32 [ntok], may be NULL): sum of squares per written row. */
+int ftl_embedding_bwd_direct(const int64_t* tokens, const int64_t* prev_tokens, const void* dout, void* dtable,
+                             int64_t ntok, int dim, int vocab, float* sumsq, ftl_stream_t stream);
 
 /* ---- Cross-entropy forward+backward in place over bf16 logits — reference: train.py:101-104 ---- */
 int ftl_cross_entropy(void* logits, const int64_t* labels, const float* inv_n, float* row_loss, float* row_lse,
@@ -76,6 +88,16 @@ int ftl_adamw_step(void* p, const void* g, void* m, void* v, int64_t n, const fl
 int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c, int64_t ldc,
                   int M, int N, int K, const void* a2, int64_t lda2, const void* b2, int64_t ldb2, int K2, int max_ctas,
                   ftl_stream_t stream);
+/* Same; sumsq (fp32 [ftl_gemm_sumsq_slots()], may be NULL) receives per-(CTA, epilogue warp) sums of squares of the
+ * stored bf16 values: the weight-gradient GEMMs emit their gradient-norm partials (reference: utils.py:58-63). */
+int ftl_gemm_sumsq_slots(void);
+int ftl_gemm_bf16_ex(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c, int64_t ldc,
+                     int M, int N, int K, const void* a2, int64_t lda2, const void* b2, int64_t ldb2, int K2,
+                     float* sumsq, int max_ctas, ftl_stream_t stream);
+/* SwiGLU backward in the epilogue of the w2 dgrad GEMM: dact = dx [M,K] @ w2 [K,H] stays in TMEM; reads the saved
+ * gate / up, writes dgate / dup (all [M,H], leading dimension ldo; H, ldo multiples of 16) — autograd of model.py:254 */
+int ftl_gemm_swiglu_bwd(const void* dx, int64_t lddx, const void* w2, int64_t ldw, const void* gate, const void* up,
+                        void* dgate, void* dup, int64_t ldo, int M, int H, int K, int max_ctas, ftl_stream_t stream);
 /* act = silu(x W1^T) * (x W3^T); gate / up (pre-activations, kept for the backward) may be NULL */
 int ftl_gemm_swiglu(const void* x, int64_t ldx, const void* w1, const void* w3, int64_t ldw, void* act, void* gate,
                     void* up, int64_t ldo, int M, int H, int K, int max_ctas, ftl_stream_t stream);

@@ -280,3 +280,76 @@ def test_attention_tc_fwd_bwd_deterministic(N, B, S, H, KV, hd):
     want = dqkv.clone()
     N.rope_inplace(want, cos, sin, S, (H + KV) * hd, hd, inverse=True)
     torch.testing.assert_close(dq3.float(), want.float(), rtol=2e-2, atol=2e-3)
+
+
+@pytest.mark.parametrize("M,H,K", [(256, 512, 256), (200, 336, 192), (2048, 14336, 4096)])
+def test_gemm_tc_swiglu_bwd_epilogue(N, M, H, K):
+    """w2 dgrad GEMM with the SwiGLU backward in its epilogue == dgrad GEMM followed by the elementwise kernel."""
+    dx, w2 = bf(M, K, scale=0.5, seed=1), bf(K, H, scale=0.1, seed=2)
+    gate, up = bf(M, H, seed=3), bf(M, H, seed=4)
+    dg, du = torch.empty_like(gate), torch.empty_like(gate)
+    N.gemm_swiglu_bwd(dx, w2, gate, up, dg, du)
+    dact = dx.float() @ w2.float()
+    gf, uf = gate.float().requires_grad_(), up.float().requires_grad_()
+    (torch.nn.functional.silu(gf) * uf).backward(dact)
+    assert _rel(dg, gf.grad) < 1e-2 and _rel(du, uf.grad) < 1e-2
+    # and bit-equal to the two-kernel path it replaces (same rounding points)
+    dact_b, dg2, du2 = torch.empty_like(gate), torch.empty_like(gate), torch.empty_like(gate)
+    N.gemm(dx, w2, dact_b, b_mn=True)
+    N.swiglu_bwd(dact_b, gate, up, dg2, du2)
+    assert torch.equal(dg, dg2) and torch.equal(du, du2)
+
+
+@pytest.mark.parametrize("M,Nn,K", [(512, 768, 256), (200, 344, 136), (4096, 4096, 2048)])
+def test_gemm_tc_sumsq_partials(N, M, Nn, K):
+    """The weight-gradient GEMM also returns sum(out^2) in deterministic pieces."""
+    dy, x = bf(K, M, scale=0.5, seed=1), bf(K, Nn, scale=0.5, seed=2)
+    out = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+    parts = torch.zeros(N.gemm_sumsq_slots(), device=DEV)
+    N.gemm(dy, x, out, a_mn=True, b_mn=True, sumsq=parts)
+    ref = out.float().pow(2).sum()
+    torch.testing.assert_close(parts.sum(), ref, rtol=1e-4, atol=1e-3)
+    parts2 = torch.zeros_like(parts)
+    N.gemm(dy, x, out, a_mn=True, b_mn=True, sumsq=parts2)
+    assert torch.equal(parts, parts2)
+
+
+def test_rmsnorm_bwd_sumsq(N):
+    rows, dim = 300, 4096
+    x, w, dy = bf(rows, dim, seed=1), bf(dim, seed=2) * 0.1 + 1, bf(rows, dim, seed=3)
+    rstd = torch.rsqrt(x.float().pow(2).mean(-1) + 1e-5)
+    dx, dw = torch.empty_like(x), torch.empty_like(w)
+    scratch = torch.empty(N.rmsnorm_partials(rows) * dim, device=DEV)
+    parts = torch.zeros(N.rmsnorm_sumsq_slots(dim), device=DEV)
+    N.rmsnorm_bwd(dy, x, w, rstd, dx, dw, scratch, sumsq=parts)
+    torch.testing.assert_close(parts.sum(), dw.float().pow(2).sum(), rtol=1e-5, atol=1e-5)
+    dw2 = torch.empty_like(w)
+    N.rmsnorm_bwd(dy, x, w, rstd, dx, dw2, scratch)
+    assert torch.equal(dw, dw2)
+
+
+@pytest.mark.parametrize("V,D,n", [(1000, 256, 4096), (50, 4096, 300), (131072, 4096, 2048)])
+def test_embedding_bwd_direct(N, V, D, n):
+    """Sort-free embedding backward: equals the fp32 index_add, is repeatable, equals the sorted kernel, clears the
+    rows only the previous step touched, and reports sum(dtable^2)."""
+    g = torch.Generator(device=DEV).manual_seed(3)
+    tok = torch.randint(0, V, (n,), device=DEV, generator=g)
+    tok[::7] = tok[0]                                   # a heavily repeated id
+    dout = bf(n, D, seed=2)
+    ref = torch.zeros(V, D, device=DEV).index_add_(0, tok, dout.float())
+    dt = torch.zeros(V, D, device=DEV, dtype=torch.bfloat16)
+    parts = torch.full((n,), 7.0, device=DEV)
+    N.embedding_bwd_direct(tok, None, dout, dt, sumsq=parts)
+    torch.testing.assert_close(dt.float(), ref, rtol=2e-2, atol=3e-2)
+    torch.testing.assert_close(parts.sum(), dt.float().pow(2).sum(), rtol=1e-4, atol=1e-3)
+    dt_sorted = torch.zeros_like(dt)
+    s, p = torch.sort(tok, stable=True)
+    N.embedding_bwd(s, p, dout, dt_sorted)
+    assert torch.equal(dt, dt_sorted)
+    # next step with other tokens: rows of the previous step that are not rewritten must end up zero
+    tok2 = torch.randint(0, V, (n,), device=DEV, generator=g)
+    dout2 = bf(n, D, seed=5)
+    N.embedding_bwd_direct(tok2, tok, dout2, dt)
+    want = torch.zeros_like(dt)
+    N.embedding_bwd_direct(tok2, None, dout2, want)
+    assert torch.equal(dt, want)
