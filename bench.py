@@ -157,7 +157,7 @@ def _measure_ours(a, env, cfg, tok, data, parallel: str, ckpt: bool) -> dict:
     if ckpt:
         res.update(_measure_checkpoint(trainer, env, stream))
     stream.close()
-    trainer.close()
+    trainer.close(release=True)
     del trainer, stream, last, fixed
     gc.collect()
     torch.cuda.empty_cache()

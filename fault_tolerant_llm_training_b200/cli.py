@@ -96,7 +96,6 @@ def build_parser() -> argparse.ArgumentParser:
           help="Periodic checkpoint interval in steps (0 = only on interruption, as the reference)")
     _flag(p, "--save-final", action="store_true",
           help="Also write a checkpoint when training completes (the reference writes none)")
-    _flag(p, "--bucket-mb", type=int, default=512, help="Gradient bucket size for dp/fsdp overlap")
     return p
 
 

@@ -167,6 +167,21 @@ class LossHandle:
         return self.item()
 
 
+class _Nvtx:
+    """NVTX ranges per phase and layer (`FTL_NVTX=1`; off by default: ~300 push/pop pairs per step cost host time)."""
+    on = os.environ.get("FTL_NVTX", "0") == "1"
+
+    @classmethod
+    def push(cls, name: str) -> None:
+        if cls.on:
+            torch.cuda.nvtx.range_push(name)
+
+    @classmethod
+    def pop(cls) -> None:
+        if cls.on:
+            torch.cuda.nvtx.range_pop()
+
+
 class NativeEngine:
     """Forward + backward of the decoder for a fixed (batch, seq) shape."""
 
@@ -349,8 +364,12 @@ class NativeEngine:
         rot = (H + KV) * hd
         self._params_waited = -1
         self._need(0)
+        _Nvtx.push("forward")
         N.embedding_fwd(tokens.view(-1), self.w_emb, self.x[0])
         for i, lw in enumerate(self.lw):
+            if i:
+                _Nvtx.pop()
+            _Nvtx.push(f"fwd layer {i}")
             self._need(i + 1)
             # residual add of the previous block fused with this block's attention_norm (x_i = h_{i-1} + ff)
             if i == 0:
@@ -378,11 +397,15 @@ class NativeEngine:
                 N.swiglu_fwd(self.gate[i], self.up[i], self.act[i])
             self.gemm_nt(self.act[i], lw["ww2"], self.ff)
         L = c.n_layers
+        _Nvtx.pop()
+        _Nvtx.push("fwd head + loss")
         self._need(L + 1)
         # x_L = h_{L-1} + ff, fused with the final norm
         N.rmsnorm_fwd(self.h[L - 1], self.w_fn, c.norm_eps, self.xf, self.rstd_f, delta=self.ff, h_out=self.x[L])
         self.gemm_nt(self.xf, self.w_out, self.logits)
         N.cross_entropy(self.logits, labels.view(-1), inv_n, self.row_loss, self.loss, write_grad=write_grad)
+        _Nvtx.pop()
+        _Nvtx.pop()
         return self.loss
 
     # ---- backward (logits already hold d loss / d logits) ---------------------------------------------
@@ -394,6 +417,8 @@ class NativeEngine:
         L = c.n_layers
         dl = self.logits
         self._arena_off = 0
+        _Nvtx.push("backward")
+        _Nvtx.push("bwd head")
         if self.hook_params_bwd is not None:
             self.hook_params_bwd(L + 1)
         self.gemm_tn(dl, self.xf, self.g_out)                     # dW_out
@@ -404,6 +429,8 @@ class NativeEngine:
             self.hook_grads(L + 1)
         for i in range(L - 1, -1, -1):
             lw = self.lw[i]
+            _Nvtx.pop()
+            _Nvtx.push(f"bwd layer {i}")
             if self.hook_params_bwd is not None:
                 self.hook_params_bwd(i + 1)
             # x_{i+1} = h + w2(act)
@@ -437,6 +464,8 @@ class NativeEngine:
         # table gradient is 1 GB and only the rows of this batch's tokens are written, so when nobody else writes into
         # it (single rank: no in-place reduction of peers' rows) the kernel itself clears the rows the PREVIOUS step
         # touched and this one does not, instead of a memset of the whole buffer.
+        _Nvtx.pop()
+        _Nvtx.push("bwd embedding")
         flat_tok = tokens.view(-1)
         prev = None
         if self.sparse_emb_zero and self._emb_dirty is not None:
@@ -450,6 +479,8 @@ class NativeEngine:
             self._emb_dirty.copy_(flat_tok)   # device-to-device copy; the kernel ignores ids outside the table
         if self.hook_grads is not None:
             self.hook_grads(0)
+        _Nvtx.pop()
+        _Nvtx.pop()
 
 
 # --------------------------------------------------------------------------------------------------
@@ -460,7 +491,7 @@ class NativeTrainer:
 
     def __init__(self, cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
                  grad_max_norm: float, clip_mode: str = "clip", seed: int = 0, parallel: str = "none",
-                 bucket_mb: int = 512, keep_shards: bool = False,
+                 keep_shards: bool = False,
                  consolidate: bool = True):
         if dtype != torch.bfloat16:
             raise ValueError("the B200 engine is bf16-only (use --device cpu for other dtypes)")
@@ -649,5 +680,5 @@ class NativeTrainer:
         self.last_grad_norm = loss.grad_norm()
         return v
 
-    def close(self) -> None:
+    def close(self, release: bool = False) -> None:
         pass

@@ -131,7 +131,7 @@ def init_dist(device_arg: str = "auto", timeout_s: int = 600) -> DistEnv:
         if not dist.is_initialized():
             # The data plane is this framework's own NVLink kernels (csrc/comm.cu); torch.distributed is only the
             # control plane (handle exchange, per-step scalars), so gloo suffices.  FTL_NCCL=1 brings NCCL up as
-            # the default group as well (needed only by the unpipelined DP schedule's moment all-gather).
+            # the default group as well (for A/B runs against library collectives).
             use_nccl = device.type == "cuda" and os.environ.get("FTL_NCCL", "0") == "1"
             kw = {"device_id": device} if use_nccl else {}
             dist.init_process_group(backend="nccl" if use_nccl else "gloo", rank=rank, world_size=world, timeout=td, **kw)

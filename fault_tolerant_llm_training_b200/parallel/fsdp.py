@@ -2,8 +2,14 @@
 the QKV and gate/up GEMMs that consume the gathered weights.
 
 Persistent state per rank is only ITS row shard of every weight matrix (one compact peer-mapped buffer),
-the matching AdamW moments, and the local gradient buffer.  Full weights exist two buckets at a time, in two
-staging slots (bucket = embedding | layer i | final norm + head):
+the matching AdamW moments, and the local gradient buffer.  Gathered weights live in staging memory, bucket by
+bucket (bucket = embedding | layer i | final norm + head), in one of two modes:
+
+  resident (default)   one staging buffer the size of the model (16 GB of the 180 GB HBM for the 8 B model): a bucket
+                       gathered for the forward is still there when the backward needs it, so every parameter
+                       crosses NVLink ONCE per step — what torch FSDP calls reshard_after_forward=False
+  reshard (FTL_FSDP_RESHARD=1)   two bucket-sized slots; the backward re-gathers each bucket one bucket ahead of
+                       the GEMMs that read it (twice the NVLink bytes, 12 GB less resident memory)
 
   forward, layer i   wo, w2 and the norm weights of the layer are gathered by the plain all-gather kernel on the
                      comm stream while the previous layer computes;  wq|wk|wv and w1, w3 — 80 % of the layer's
@@ -11,7 +17,8 @@ staging slots (bucket = embedding | layer i | final norm + head):
                      pull the owners' rows over NVLink from inside the GEMM (the epilogue warps of every CTA
                      move 16-row slices while they wait for accumulators; the TMA producers wait per 128-row
                      half block), so the transfer overlaps the MMAs tile by tile
-  backward, layer i  the whole bucket is re-gathered (plain kernel, one bucket ahead of the backward GEMMs)
+  backward, layer i  resident mode: nothing to fetch.  reshard mode: the whole bucket is re-gathered (plain kernel,
+                     one bucket ahead of the backward GEMMs)
   update             gradient reduce-scatter ⊕ norm² per shard under backward, then clip ⊕ AdamW on the compact
                      shards; no parameter all-gather follows — the next forward reads the shards directly
 
@@ -41,23 +48,22 @@ class _Unit:
 
 
 class FsdpState(FlatState):
-    """Flat gradient buffer as usual; parameters are views into the two staging slots (by bucket parity)."""
+    """Flat gradient buffer as usual; parameters are views into the staging memory: `slot_of(bucket)` returns the
+    staging tensor that holds the bucket and the flat offset of its first element."""
 
-    def bind_slots(self, slots: List[torch.Tensor], bucket_of: Dict[str, int], bucket_lo: List[int]) -> None:
-        self._slots, self._bucket_of, self._bucket_lo = slots, bucket_of, bucket_lo
+    def bind_slots(self, slot_of, bucket_of: Dict[str, int]) -> None:
+        self._slot_of, self._bucket_of = slot_of, bucket_of
 
     def param_view(self, name: str) -> torch.Tensor:
         off, n, shape = self.index[name]
-        b = self._bucket_of[name]
-        rel = off - self._bucket_lo[b]
-        return self._slots[b % 2][rel:rel + n].view(shape)
+        buf, base = self._slot_of(self._bucket_of[name])
+        return buf[off - base:off - base + n].view(shape)
 
     def param_span(self, first: str, last: str, shape) -> torch.Tensor:
         o0, _, _ = self.index[first]
         o1, n1, _ = self.index[last]
-        b = self._bucket_of[first]
-        rel = o0 - self._bucket_lo[b]
-        return self._slots[b % 2][rel:rel + (o1 + n1 - o0)].view(shape)
+        buf, base = self._slot_of(self._bucket_of[first])
+        return buf[o0 - base:o1 + n1 - base].view(shape)
 
 
 class FsdpTrainer(PipelinedTrainer):
@@ -118,7 +124,12 @@ class FsdpTrainer(PipelinedTrainer):
         self.p_own = self.symm.tensor("own", torch.bfloat16)
         self.m_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
         self.v_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
-        self.stage = [torch.zeros(max_bucket, dtype=torch.bfloat16, device=self.device) for _ in range(2)]
+        import os
+        self.reshard = os.environ.get("FTL_FSDP_RESHARD", "0") == "1"
+        if self.reshard:   # two bucket-sized slots, by bucket parity
+            self.stage = [torch.zeros(max_bucket, dtype=torch.bfloat16, device=self.device) for _ in range(2)]
+        else:              # the whole model stays gathered from its forward until its update
+            self.stage = [torch.zeros(numel, dtype=torch.bfloat16, device=self.device)]
         # ---- move the freshly initialised parameters into the shards, then drop the full copies
         with torch.no_grad():
             params = dict(self.model.named_parameters())
@@ -142,7 +153,7 @@ class FsdpTrainer(PipelinedTrainer):
         bucket_of = {}
         for name, (off, n, shape) in index.items():
             bucket_of[name] = max(b for b, (lo, hi) in enumerate(self.buckets) if lo <= off)
-        flat.bind_slots(self.stage, bucket_of, [lo for lo, _ in self.buckets])
+        flat.bind_slots(self._slot_of, bucket_of)
         with torch.no_grad():
             for name, prm in self.model.named_parameters():
                 off, n, shape = index[name]
@@ -151,10 +162,12 @@ class FsdpTrainer(PipelinedTrainer):
         self._finish_pipeline_state(flat)
         # ---- staging-slot bookkeeping
         NB = L + 2
-        self.resident = [-1, -1]            # bucket currently in each slot
-        self.resident_full = [False, False]  # ... including the matrices the fused GEMMs gather themselves
+        ns = 2 if self.reshard else NB
+        self.resident = [-1] * ns            # bucket currently in each slot
+        self.resident_full = [False] * ns    # ... including the matrices the fused GEMMs gather themselves
         self.ev_gather = [torch.cuda.Event() for _ in range(NB)]
-        self.ev_slot_free = [torch.cuda.Event(), torch.cuda.Event()]
+        self.ev_slot_free = [torch.cuda.Event() for _ in range(ns)]
+        self.gather_stream = torch.cuda.Stream(device=self.device, priority=-1)
         self.gather_scratch = torch.zeros(1 + 2 * (self.cfg.ffn_hidden // 128 + self.cfg.qkv_dim // 128 + 2),
                                           dtype=torch.int32, device=self.device)
         return flat
@@ -182,6 +195,14 @@ class FsdpTrainer(PipelinedTrainer):
         self._params_pending = False
         self._hyper = None
 
+    def _k(self, b: int) -> int:
+        """Staging slot index of bucket b."""
+        return b % 2 if self.reshard else b
+
+    def _slot_of(self, b: int):
+        """(staging tensor, flat offset of its first element) for bucket b."""
+        return (self.stage[b % 2], self.buckets[b][0]) if self.reshard else (self.stage[0], 0)
+
     def _owned_ranges(self, flat) -> List[List[Tuple[int, int]]]:
         r = self.env.rank
         return [[(u.off + r * u.shard, u.off + (r + 1) * u.shard) for u in us] for us in self.bucket_units]
@@ -191,20 +212,25 @@ class FsdpTrainer(PipelinedTrainer):
         """Enqueue (comm stream) the plain all-gather of bucket b into staging slot b % 2, unless it is there already.
         The caller guarantees that every kernel reading the slot's previous occupant has been enqueued on the main
         stream: an event recorded there now is what the gather waits for."""
-        k = b % 2
+        k = self._k(b)
         have = self.resident[k] == b
         if have and (self.resident_full[k] or not include_fused):
             return
-        env, lo = self.env, self.buckets[b][0]
+        env = self.env
+        buf, lo = self._slot_of(b)
         if not have:
             self.ev_slot_free[k].record()                      # main stream: previous occupant no longer needed
-        with torch.cuda.stream(self.comm):
+        # Gathers run on their own stream: on the comm stream they would queue behind the AdamW kernels of EVERY
+        # bucket of the previous step, and the forward could not start before the whole update had finished.
+        with torch.cuda.stream(self.gather_stream):
             if not have:
-                self.comm.wait_event(self.ev_slot_free[k])
+                self.gather_stream.wait_event(self.ev_slot_free[k])
+            if self._params_pending:
+                self.gather_stream.wait_event(self.ev_param[b])   # bucket b's shards are updated on every rank
             for u in self.bucket_units[b]:
                 if (u.fused and not include_fused) or (have and not u.fused):
                     continue
-                N.fsdp_gather(self.symm.table("own"), u.coff, self.stage[k][u.off - lo:u.off - lo + u.numel], u.shard,
+                N.fsdp_gather(self.symm.table("own"), u.coff, buf[u.off - lo:u.off - lo + u.numel], u.shard,
                               env.rank, env.world_size, self.comm_status, max_ctas=self.GATHER_CTAS)
             self.ev_gather[b].record()
         self.resident[k] = b
@@ -249,7 +275,7 @@ class FsdpTrainer(PipelinedTrainer):
         N.gemm_swiglu_gather(x, e.lw[i]["ww1"], e.lw[i]["ww3"], act, gate, up, self.symm.table("own"), lu["w1"].coff,
                              lu["w3"].coff, lu["w1"].rows // self.env.world_size, self.env.rank, self.env.world_size,
                              self.gather_scratch)
-        self.resident_full[(i + 1) % 2] = True        # wq|wk|wv, w1, w3 of this layer are now in the slot too
+        self.resident_full[self._k(i + 1)] = True     # wq|wk|wv, w1, w3 of this layer are now in the slot too
 
     # ---- update: AdamW on the compact shards, no all-gather -----------------------------------------------------
     def _update_bucket(self, b: int, hyper: torch.Tensor) -> None:
@@ -261,7 +287,7 @@ class FsdpTrainer(PipelinedTrainer):
                           self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
 
     def _after_update(self, b: int) -> None:
-        k = b % 2
+        k = self._k(b)
         if self.resident[k] == b:
             self.resident[k] = -1                      # the staged copy of bucket b is stale now
 
@@ -305,7 +331,7 @@ class FsdpTrainer(PipelinedTrainer):
             self.env.barrier()
         else:
             super().load_state(ckpt)
-        self.resident = [-1, -1]
+        self.resident = [-1] * len(self.resident)
 
     def full_parameters(self) -> Dict[str, torch.Tensor]:
         """All-gather every parameter (testing / export); not used on the training path."""

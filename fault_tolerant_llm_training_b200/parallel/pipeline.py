@@ -199,5 +199,10 @@ class PipelinedTrainer(NativeTrainer):
         torch.cuda.synchronize()
         self.env.barrier()
 
-    def close(self) -> None:
+    def close(self, release: bool = False) -> None:
+        """release=True also frees the peer-mapped buffers (a collective; for processes that build another trainer
+        afterwards, e.g. bench.py).  The training driver leaves that to process exit: after a failure a collective
+        in the exit path could wait for a rank that is gone."""
         torch.cuda.synchronize()
+        if release:
+            self.symm.close()

@@ -7,6 +7,7 @@ rank.  The reference has no communication layer to compare with (SURVEY ยง2.3, ย
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Dict, List
 
 import torch
@@ -44,6 +45,23 @@ class SymmetricBuffers:
             self.tables[name] = torch.tensor(ptrs, dtype=torch.int64, device=env.device)
         self.sizes = dict(sizes)
         env.barrier()
+
+    def close(self) -> None:
+        """Unmap the peers' buffers and free the own ones.  Collective: every rank has stopped using every buffer
+        (the caller synchronised its device) before anything is released; tensors handed out by `tensor()` must not
+        be touched afterwards."""
+        if not self.local_ptr:
+            return
+        env = self.env
+        env.barrier()
+        for name, ptrs in self.peer_ptr.items():
+            for r, p in enumerate(ptrs):
+                if r != env.rank:
+                    N.lib().ftl_ipc_close(ctypes.c_void_p(p))
+        env.barrier()            # nobody maps my memory any more
+        for p in self.local_ptr.values():
+            N.lib().ftl_symm_free(ctypes.c_void_p(p))
+        self.local_ptr, self.peer_ptr, self.tables, self._holders = {}, {}, {}, []
 
     def tensor(self, name: str, dtype: torch.dtype) -> torch.Tensor:
         """Local buffer `name` as a torch tensor (no copy, not owned by torch's allocator)."""

@@ -84,7 +84,7 @@ def train(args) -> None:
     trainer = make_trainer(cfg, env, dtype=model_dtype, lr=args.learning_rate,
                            warmup_steps=args.lr_warmup_steps, grad_max_norm=args.grad_max_norm,
                            clip_mode=args.clip_mode, seed=args.seed, parallel=args.parallel,
-                           fused_optimizer=args.fused_optimizer, bucket_mb=args.bucket_mb,
+                           fused_optimizer=args.fused_optimizer,
                            keep_shards=args.sharded_checkpoint,
                            consolidate=not args.no_consolidate, compile_model=args.compile)
     if args.compile:
@@ -110,6 +110,11 @@ def train(args) -> None:
 
     tokens_per_step = args.batch_size * args.sequence_length * env.world_size
     t_window, window_steps = time.perf_counter(), 0
+    # Device-side step timer: a CUDA event is recorded on the compute stream at every logging step; the
+    # time between the two most recent COMPLETED events is reported one window late, so the host never waits for it.
+    on_gpu = env.device.type == "cuda"
+    dev_marks = []   # [(event, steps in the window that ended there)]
+    nvtx = torch.cuda.nvtx if on_gpu else None
     exit_kw = dict(rank=env.rank, world_size=env.world_size, resubmit_cmd=args.resubmit_cmd,
                    resume_id=args.checkpoint_id, flags=flags)
     # FTL_INJECT_RANK_ERROR="rank:step" raises on one rank only (test hook for the peer-failure path)
@@ -142,18 +147,31 @@ def train(args) -> None:
             if code != STOP_NONE:
                 agreed = True
                 raise TrainingInterrupt(stop_code_to_error_type(code))
+            if nvtx is not None:
+                nvtx.range_push(f"step {training_step}")
             loss = trainer.step(input_ids, labels, n_items=n_items)
+            if nvtx is not None:
+                nvtx.range_pop()
 
             window_steps += 1
             if training_step == 1 or training_step % args.logging_frequency == 0:
+                if on_gpu:
+                    ev = torch.cuda.Event(enable_timing=True)
+                    ev.record()
+                    dev_marks.append((ev, window_steps))
                 loss_val = trainer.loss_value(loss)  # device -> host sync, as loss.item() in train.py:116
                 now = time.perf_counter()
                 ms = (now - t_window) * 1e3 / max(window_steps, 1)
+                dev = ""
+                if len(dev_marks) >= 3 and dev_marks[-2][0].query():   # previous window: both of its events are done
+                    dms = dev_marks[-3][0].elapsed_time(dev_marks[-2][0]) / max(dev_marks[-2][1], 1)
+                    dev = f" | device {dms:.1f} ms/step (previous window, CUDA events)"
+                    del dev_marks[:-2]
                 logger.info(f"Training step: {training_step} | Loss: {loss_val:.2f}")
                 logger.info(f"  step {training_step}: loss {loss_val:.6f} | {ms:.1f} ms/step | "
                             f"{tokens_per_step / max(ms, 1e-9) * 1e3:.0f} tokens/s | "
                             f"lr {trainer.optimizer.param_groups[0]['lr']:.4e} | "
-                            f"grad_norm {float(trainer.last_grad_norm):.4f}")
+                            f"grad_norm {float(trainer.last_grad_norm):.4f}{dev}")
                 t_window, window_steps = time.perf_counter(), 0
             training_step += 1
         # One more agreement after the last step: a rank that fails locally during its final step (or while its peers

@@ -97,13 +97,13 @@ class TorchTrainer:
     def loss_value(self, loss: torch.Tensor) -> float:
         return float(loss.item())
 
-    def close(self) -> None:
+    def close(self, release: bool = False) -> None:
         pass
 
 
 def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: float, warmup_steps: int,
                  grad_max_norm: float = 1.0, clip_mode: str = "clip", seed: int = 0, parallel: str = "auto",
-                 fused_optimizer: bool = False, bucket_mb: int = 512,
+                 fused_optimizer: bool = False,
                  force_torch: bool = False, keep_shards: bool = False, consolidate: bool = True,
                  compile_model: bool = False):
     """Factory used by train.py, bench.py and the tests."""
@@ -114,18 +114,15 @@ def make_trainer(cfg: ModelConfig, env: DistEnv, *, dtype: torch.dtype, lr: floa
 
         if env.distributed and parallel == "none":
             raise ValueError("--parallel none with WORLD_SIZE > 1: ranks would train unsynchronised copies")
-        import os
         if parallel == "fsdp":
             from .parallel.fsdp import FsdpTrainer as NativeTrainer  # noqa: F811
-        elif os.environ.get("FTL_PIPELINE", "1") != "0":
-            # default: bucketed, overlapped reduce-scatter / AdamW / all-gather on a second stream (1..8 GPUs)
+        else:
+            # bucketed, overlapped reduce-scatter / AdamW / all-gather on a second stream (1..8 GPUs)
             from .parallel.pipeline import PipelinedTrainer as NativeTrainer  # noqa: F811
-        elif env.distributed:
-            from .parallel.dp import DPNativeTrainer as NativeTrainer  # noqa: F811 (unpipelined reference schedule)
 
         return NativeTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps,
                              grad_max_norm=grad_max_norm, clip_mode=clip_mode, seed=seed,
-                             parallel=parallel, bucket_mb=bucket_mb,
+                             parallel=parallel,
                              keep_shards=keep_shards, consolidate=consolidate)
     return TorchTrainer(cfg, env, dtype=dtype, lr=lr, warmup_steps=warmup_steps, grad_max_norm=grad_max_norm,
                         clip_mode=clip_mode, seed=seed, fused_optimizer=fused_optimizer, compile_model=compile_model)
