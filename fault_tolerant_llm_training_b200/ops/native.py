@@ -91,6 +91,19 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_rmsnorm_sumsq_slots", [I])
     _sig(L, "ftl_rmsnorm_bwd_ex", [P, P, P, P, P, P, P, P, P, I, I, P])
     _sig(L, "ftl_embedding_bwd_direct", [P, P, P, P, I64, I, I, P, P])
+    U64P, IP = ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(c_int)
+    _sig(L, "ftl_vmm_supported", [IP, IP])
+    _sig(L, "ftl_vmm_round", [I64, I], c_int64)
+    _sig(L, "ftl_vmm_alloc", [I64, PP, U64P, IP])
+    _sig(L, "ftl_vmm_import", [I, I64, PP, U64P])
+    _sig(L, "ftl_vmm_unmap", [P, I64, ctypes.c_uint64])
+    _sig(L, "ftl_fd_close", [I])
+    _sig(L, "ftl_mc_create", [I, I64, U64P, IP])
+    _sig(L, "ftl_mc_import", [I, U64P])
+    _sig(L, "ftl_mc_add_device", [ctypes.c_uint64])
+    _sig(L, "ftl_mc_bind_map", [ctypes.c_uint64, ctypes.c_uint64, I64, PP])
+    _sig(L, "ftl_nvls_reduce_scatter", [P, P, I64, I64, P, P, I, P])
+    _sig(L, "ftl_nvls_adamw_allgather", [P, P, P, P, P, I64, I64, P, P, P, P, I, P])
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -356,6 +369,79 @@ def dp_adamw_allgather(peer_p, g, m, v, rank, world, lo, n, hyper, stats, status
     _check(lib().ftl_dp_adamw_allgather(_ptr(peer_p), _ptr(g), _ptr(m), _ptr(v), rank, world, lo, n, _ptr(hyper),
                                         _ptr(stats), _ptr(status), _ptr(commits), max_ctas, _stream()),
            "ftl_dp_adamw_allgather")
+
+
+# ---- VMM symmetric heap + NVLS multicast (csrc/nvls.cu) ------------------------------------------------------
+def _drv(code: int, what: str) -> None:
+    if code != 0:
+        kind = f"CUDA driver error {code - 1000}" if code >= 1000 else f"CUDA error {code}"
+        raise NativeError(f"{what} failed with {kind}")
+
+
+def vmm_supported():
+    """(vmm, multicast): the virtual-memory API with fd export / multicast objects are usable on the current device."""
+    a, b = c_int(0), c_int(0)
+    _drv(lib().ftl_vmm_supported(ctypes.byref(a), ctypes.byref(b)), "ftl_vmm_supported")
+    return bool(a.value), bool(b.value)
+
+
+def vmm_round(nbytes: int, world: int) -> int:
+    r = lib().ftl_vmm_round(nbytes, world)
+    if r < 0:
+        raise NativeError("ftl_vmm_round: the CUDA virtual-memory API is not available")
+    return r
+
+
+def vmm_alloc(nbytes: int):
+    """-> (device pointer, allocation handle, exportable file descriptor)"""
+    ptr, h, fd = c_void_p(), ctypes.c_uint64(0), c_int(-1)
+    _drv(lib().ftl_vmm_alloc(nbytes, ctypes.byref(ptr), ctypes.byref(h), ctypes.byref(fd)), f"ftl_vmm_alloc({nbytes})")
+    return ptr.value, h.value, fd.value
+
+
+def vmm_import(fd: int, nbytes: int):
+    ptr, h = c_void_p(), ctypes.c_uint64(0)
+    _drv(lib().ftl_vmm_import(fd, nbytes, ctypes.byref(ptr), ctypes.byref(h)), "ftl_vmm_import")
+    return ptr.value, h.value
+
+
+def vmm_unmap(ptr: int, nbytes: int, handle: int) -> None:
+    _drv(lib().ftl_vmm_unmap(c_void_p(ptr), nbytes, ctypes.c_uint64(handle)), "ftl_vmm_unmap")
+
+
+def mc_create(world: int, nbytes: int):
+    h, fd = ctypes.c_uint64(0), c_int(-1)
+    _drv(lib().ftl_mc_create(world, nbytes, ctypes.byref(h), ctypes.byref(fd)), "cuMulticastCreate")
+    return h.value, fd.value
+
+
+def mc_import(fd: int) -> int:
+    h = ctypes.c_uint64(0)
+    _drv(lib().ftl_mc_import(fd, ctypes.byref(h)), "multicast import")
+    return h.value
+
+
+def mc_add_device(mc: int) -> None:
+    _drv(lib().ftl_mc_add_device(ctypes.c_uint64(mc)), "cuMulticastAddDevice")
+
+
+def mc_bind_map(mc: int, mem: int, nbytes: int) -> int:
+    ptr = c_void_p()
+    _drv(lib().ftl_mc_bind_map(ctypes.c_uint64(mc), ctypes.c_uint64(mem), nbytes, ctypes.byref(ptr)), "cuMulticastBindMem / map")
+    return ptr.value
+
+
+def nvls_reduce_scatter(mc_g: int, g_local, lo, n, partial, status, max_ctas=0):
+    """Reduce-scatter of shard [lo, lo+n) through the switch: multimem.ld_reduce from the multicast address mc_g."""
+    _check(lib().ftl_nvls_reduce_scatter(c_void_p(mc_g), _ptr(g_local), lo, n, _ptr(partial), _ptr(status), max_ctas,
+                                         _stream()), "ftl_nvls_reduce_scatter")
+
+
+def nvls_adamw_allgather(mc_p: int, p_local, g, m, v, lo, n, hyper, stats, status, commits=None, max_ctas=0):
+    """clip + AdamW on [lo, lo+n) with the all-gather as ONE multimem.st per vector through the multicast address mc_p."""
+    _check(lib().ftl_nvls_adamw_allgather(c_void_p(mc_p), _ptr(p_local), _ptr(g), _ptr(m), _ptr(v), lo, n, _ptr(hyper),
+                                          _ptr(stats), _ptr(status), _ptr(commits), max_ctas, _stream()),
+           "ftl_nvls_adamw_allgather")
 
 
 # ---- checkpoint snapshot engine (csrc/ckpt_io.cu) -----------------------------------------------------

@@ -28,6 +28,7 @@ The reference has no counterpart.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Tuple
 
 import torch
@@ -35,7 +36,7 @@ import torch
 from ..models.engine import FlatState
 from ..ops import native as N
 from .pipeline import PipelinedTrainer
-from .symm import SymmetricBuffers
+from .symm import make_symmetric
 
 
 class _Unit:
@@ -120,7 +121,10 @@ class FsdpTrainer(PipelinedTrainer):
         self.own_numel = (coff + 1023) // 1024 * 1024
         max_bucket = max(hi - lo for lo, hi in self.buckets)
         flag_words = N.lib().ftl_comm_flag_words()
-        self.symm = SymmetricBuffers(env, {"own": self.own_numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64})
+        # fully-sharded mode has no parameter broadcast; its gradient reduce-scatter can go through the switch too
+        self.nvls = os.environ.get("FTL_COLLECTIVE", "p2p") == "nvls" and W > 1
+        self.symm = make_symmetric(env, {"own": self.own_numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64},
+                                   multicast=("g",) if self.nvls else ())
         self.p_own = self.symm.tensor("own", torch.bfloat16)
         self.m_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
         self.v_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)

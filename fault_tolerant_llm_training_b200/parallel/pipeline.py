@@ -27,7 +27,7 @@ import torch
 
 from ..models.engine import FlatState, LossHandle, NativeTrainer
 from ..ops import native as N
-from .symm import SymmetricBuffers
+from .symm import make_symmetric
 
 
 class PipelinedTrainer(NativeTrainer):
@@ -44,7 +44,12 @@ class PipelinedTrainer(NativeTrainer):
         layout = param_layout(self.model)
         numel = (flat_size(layout) + 1023) // 1024 * 1024
         flag_words = N.lib().ftl_comm_flag_words()
-        self.symm = SymmetricBuffers(env, {"p": numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64})
+        # FTL_COLLECTIVE=p2p (default): fixed-order peer loads / stores, bitwise reproducible — what kill/resume chains
+        # need.  FTL_COLLECTIVE=nvls: the reduction and the broadcast are done by the NVSwitch (multimem instructions on
+        # a multicast mapping of p and g); fewer NVLink bytes, summation order up to the switch.
+        self.nvls = os.environ.get("FTL_COLLECTIVE", "p2p") == "nvls" and W > 1
+        self.symm = make_symmetric(env, {"p": numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64},
+                                   multicast=("p", "g") if self.nvls else ())
         bufs = {"p": lambda n: self.symm.tensor("p", torch.bfloat16), "g": lambda n: self.symm.tensor("g", torch.bfloat16)}
         flat = FlatState(self.model, self.device, buffers=bufs, pad_to=1024)
         assert flat.numel == numel
@@ -122,8 +127,12 @@ class PipelinedTrainer(NativeTrainer):
             self._barrier()          # every rank's bucket-b gradients are complete
             for (a, e), k in zip(self.ranges[b], self.range_slot[b]):
                 part = self.rs_partials[k * self.parts:(k + 1) * self.parts]
-                N.dp_reduce_scatter(self.symm.table("g"), self.env.rank, self.env.world_size, a, e - a, part,
-                                    self.comm_status, max_ctas=self.RS_LAST_CTAS if b == 0 else self.RS_CTAS)
+                ctas = self.RS_LAST_CTAS if b == 0 else self.RS_CTAS
+                if getattr(self, "nvls", False):
+                    N.nvls_reduce_scatter(self.symm.mc_ptr["g"], self.flat.g, a, e - a, part, self.comm_status, max_ctas=ctas)
+                else:
+                    N.dp_reduce_scatter(self.symm.table("g"), self.env.rank, self.env.world_size, a, e - a, part,
+                                        self.comm_status, max_ctas=ctas)
 
     # ---- step pieces ---------------------------------------------------------------------------------------------
     def _begin_step(self, hyper: torch.Tensor) -> None:
@@ -153,8 +162,12 @@ class PipelinedTrainer(NativeTrainer):
         """clip ⊕ AdamW ⊕ all-gather of this rank's ranges of bucket b (runs on the comm stream)."""
         f, env = self.flat, self.env
         for a, e in self.ranges[b]:
-            N.dp_adamw_allgather(self.symm.table("p"), f.g, f.m, f.v, env.rank, env.world_size, a, e - a, hyper,
-                                 self.stats, self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
+            if getattr(self, "nvls", False):
+                N.nvls_adamw_allgather(self.symm.mc_ptr["p"], f.p, f.g, f.m, f.v, a, e - a, hyper, self.stats,
+                                       self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
+            else:
+                N.dp_adamw_allgather(self.symm.table("p"), f.g, f.m, f.v, env.rank, env.world_size, a, e - a, hyper,
+                                     self.stats, self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
 
     def _after_update(self, b: int) -> None:
         pass

@@ -129,6 +129,33 @@ int ftl_attn_bwd(const void* qkv, int64_t ld_qkv, const void* out, const void* d
                  float* delta, void* dqkv, const float* cos_t, const float* sin_t, float* scratch, int B, int S, int H,
                  int KV, int hd, ftl_stream_t stream);
 
+/* ---- Symmetric heap on the CUDA virtual-memory API + NVSwitch multicast (csrc/nvls.cu) --------------------------------
+ * No counterpart in the reference (single process, no communication: train.py:16 is its only rank-related line).
+ * Every rank allocates with ftl_vmm_alloc and passes the returned file descriptor to its peers (unix socket,
+ * SCM_RIGHTS); peers map it with ftl_vmm_import.  Sizes must be rounded with ftl_vmm_round first.  Return codes
+ * >= 1000 are 1000 + CUresult.  A multicast object (one rank creates, all import, all add their device, then all bind
+ * their own allocation and map) yields an address at which multimem.st writes every rank's copy and multimem.ld_reduce
+ * returns the sum of all copies, computed in the switch. */
+int ftl_vmm_supported(int* vmm, int* multicast);
+int64_t ftl_vmm_round(int64_t bytes, int world);
+int ftl_vmm_alloc(int64_t bytes, void** ptr, uint64_t* handle, int* fd);   /* set-up time only: allocates */
+int ftl_vmm_import(int fd, int64_t bytes, void** ptr, uint64_t* handle);
+int ftl_vmm_unmap(void* ptr, int64_t bytes, uint64_t handle);
+int ftl_fd_close(int fd);
+int ftl_mc_create(int world, int64_t bytes, uint64_t* mc, int* fd);
+int ftl_mc_import(int fd, uint64_t* mc);
+int ftl_mc_add_device(uint64_t mc);
+int ftl_mc_bind_map(uint64_t mc, uint64_t mem, int64_t bytes, void** ptr);
+/* NVLS variants of the two fused collectives below: mc_g / mc_p are the multicast addresses of the gradient / parameter
+ * buffers.  The reduce-scatter reads shard [lo, lo+n) with multimem.ld_reduce (fp32 accumulation in the switch) into
+ * g_local and emits the sum-of-squares partials; the update stores each new 16-byte parameter vector once with
+ * multimem.st.  Summation order is the switch's: use the peer-load kernels when bitwise reproducibility matters. */
+int ftl_nvls_reduce_scatter(const void* mc_g, void* g_local, int64_t lo, int64_t n, float* partial, const void* status,
+                            int max_ctas, ftl_stream_t stream);
+int ftl_nvls_adamw_allgather(void* mc_p, const void* p_local, const void* g, void* m, void* v, int64_t lo, int64_t n,
+                             const float* hyper, const float* stats, const void* status, void* commits, int max_ctas,
+                             ftl_stream_t stream);
+
 /* ---- NVLink data plane (csrc/comm.cu): symmetric buffers over CUDA IPC, device barriers, fused collectives -----------
  * peer_* arguments are device arrays of `world` pointers (this rank's own buffer at index `rank`).
  * status: device uint32, 0 ok / 1 barrier timed out / 2 a peer raised the abort word; sticky, every kernel below becomes

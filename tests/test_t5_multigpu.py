@@ -98,3 +98,31 @@ def test_comm_stress_barrier_timeout_and_delays():
     res = out[-1]
     assert res["barrier_epochs_ok"] and res["gather_gemm_ok"] and res["timeout_status"] == 1 and res["untouched_after_timeout"], res
     assert res["abort_status"] == 2, res
+
+
+def _multicast_ok() -> bool:
+    from fault_tolerant_llm_training_b200.ops import native
+    try:
+        torch.cuda.set_device(0)
+        return native.vmm_supported()[1]
+    except Exception:  # noqa: BLE001
+        return False
+
+
+@needs2
+def test_vmm_heap_dp_tracks_one_gpu():
+    """Symmetric heap built with cuMemCreate + fd passing + cuMemMap instead of CUDA IPC; same peer-load kernels."""
+    r, out = _torchrun(2, "tools/dp_check.py", env={"FTL_SYMM": "vmm"})
+    assert r.returncode == 0 and out and out[0]["ok"] and out[0]["ranks_identical"], r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@needs2
+@pytest.mark.parametrize("world", WORLDS or [2])
+def test_nvls_collectives_track_one_gpu(world):
+    """FTL_COLLECTIVE=nvls: multimem.ld_reduce reduce-scatter and multimem.st all-gather through a multicast mapping."""
+    if not _multicast_ok():
+        pytest.skip("multicast objects (NVLS) are not supported on this GPU / driver")
+    r, out = _torchrun(world, "tools/dp_check.py", env={"FTL_COLLECTIVE": "nvls"})
+    assert r.returncode == 0 and out and out[0]["ok"] and out[0]["ranks_identical"], r.stdout[-2000:] + r.stderr[-2000:]
+    r, out = _torchrun(world, "tools/fsdp_check.py", env={"FTL_COLLECTIVE": "nvls"})
+    assert r.returncode == 0 and out and out[0]["ok"], r.stdout[-2000:] + r.stderr[-2000:]
