@@ -41,7 +41,9 @@ __device__ __forceinline__ int4 ld_peer16(const void* p) {
     return r;
 }
 
-// status word: 0 ok, 1 barrier timed out, 2 a peer raised the abort word.  Sticky until the host clears it.
+// status word: 0 ok, 1 barrier timed out, 2 a peer raised the abort word, 3 the global gradient norm was not finite.
+// Sticky until the host clears it: once it is non-zero NO later update is applied, so the device state stays that of the
+// last good step however far ahead the host has already enqueued.
 // flags layout per rank (uint32): [0..W) arrival epochs written by peers, [kMaxRanks] abort word.
 __global__ void barrier_kernel(uint32_t* const* __restrict__ peer_flags, int rank, int world, uint32_t epoch,
                                uint32_t* __restrict__ status, uint64_t timeout_ns) {
@@ -116,7 +118,8 @@ __global__ void publish_kernel(const float* __restrict__ partial, int nparts, co
 }
 
 __global__ void dp_finalize_kernel(const float* __restrict__ slots, int world, const float* __restrict__ hyper,
-                                   float* __restrict__ stats, float* __restrict__ loss_out, int clip) {
+                                   float* __restrict__ stats, float* __restrict__ loss_out, int clip,
+                                   uint32_t* __restrict__ status) {
     if (threadIdx.x != 0) return;
     float total = 0.f, loss = 0.f;
     for (int r = 0; r < world; ++r) {   // same order on every rank -> bitwise-identical norm everywhere
@@ -129,6 +132,9 @@ __global__ void dp_finalize_kernel(const float* __restrict__ slots, int world, c
     if (clip && finite) coef = fminf(1.f, hyper[7] / (norm + 1e-6f));
     stats[0] = norm; stats[1] = coef; stats[2] = finite ? 1.f : 0.f; stats[3] = total;
     if (loss_out) loss_out[0] = loss;
+    // every rank folds the same slots in the same order, so all of them gate the same step (reference: the step that
+    // meets a non-finite norm raises before optimizer.step(), utils.py:61, train.py:104-107)
+    if (!finite && status) atomicMax(status, 3u);
 }
 
 template <int W>
@@ -287,8 +293,8 @@ FTL_API int ftl_dp_publish(const float* partial, int nparts, const float* loss_l
 }
 
 FTL_API int ftl_dp_finalize(const float* slots, int world, const float* hyper, float* stats, float* loss_out, int clip,
-                            cudaStream_t stream) {
-    dp_finalize_kernel<<<1, 32, 0, stream>>>(slots, world, hyper, stats, loss_out, clip);
+                            void* status, cudaStream_t stream) {
+    dp_finalize_kernel<<<1, 32, 0, stream>>>(slots, world, hyper, stats, loss_out, clip, (uint32_t*)status);
     FTL_LAUNCH_CHECK();
     return 0;
 }

@@ -603,10 +603,10 @@ class NativeTrainer:
     def _inspect(self, old: "LossHandle") -> None:
         """Host-side check of a finished step (two steps late, see step())."""
         old.event.synchronize()
-        if old.host[4] != 0.0:
+        if old.host[4] not in (0.0, 3.0):   # 3 = non-finite norm, reported below with the reference's message
             from ..ft.signals import PeerAbort
             raise PeerAbort(f"collective step aborted (status {int(old.host[4])}: 1 = barrier timeout, 2 = peer abort)")
-        if not old.finite():
+        if not old.finite() or old.host[4] == 3.0:
             raise FloatingPointError("The total norm of gradients is non-finite, so it cannot be clipped.")
         self.last_grad_norm = old.grad_norm()
 

@@ -147,7 +147,7 @@ class PipelinedTrainer(NativeTrainer):
             parts = self.engine.norm_arena if getattr(self, "fused_norm", False) else self.rs_partials
             N.dp_publish(parts, parts.numel(), loss, self.symm.table("slots"), env.rank, W)
             self._barrier()          # all slots written; nobody still reads my gradients for phase 1
-            N.dp_finalize(self.slots, W, hyper, self.stats, loss, clip=(self.clip_mode == "clip"))
+            N.dp_finalize(self.slots, W, hyper, self.stats, loss, clip=(self.clip_mode == "clip"), status=self.comm_status)
             self._result_handle = self._publish_result_on_comm(loss)
             for b in range(len(self.buckets)):
                 self._update_bucket(b, hyper)
