@@ -145,13 +145,23 @@ nvls_reduce_scatter_kernel(const __nv_bfloat16* __restrict__ mc_g, __nv_bfloat16
     if (*status == 0) {
         const __nv_bfloat16* src = mc_g + lo_vec * 8;
         __nv_bfloat16* dst = g_local + lo_vec * 8;
-        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-            const bf16x8 s = mm_ld_reduce_add(src + i * 8);    // sum over the W copies, formed in the switch (fp32)
-            st8(dst + i * 8, s);
-            float f[8];
-            unpack8(s, f);
+        // four independent switch reductions in flight per thread (the round trip through the switch is long)
+        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+        for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < nvec; i0 += 4 * stride) {
+            bf16x8 s[4];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc += f[j] * f[j];
+            for (int u = 0; u < 4; ++u)
+                if (i0 + u * stride < nvec) s[u] = mm_ld_reduce_add(src + (i0 + u * stride) * 8);   // fp32 sum over W copies
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (i0 + u * stride < nvec) {
+                    st8(dst + (i0 + u * stride) * 8, s[u]);
+                    float f[8];
+                    unpack8(s[u], f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc += f[j] * f[j];
+                }
+            }
         }
     }
     const float total = block_sum(acc, red);

@@ -128,7 +128,6 @@ class FsdpTrainer(PipelinedTrainer):
         self.p_own = self.symm.tensor("own", torch.bfloat16)
         self.m_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
         self.v_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
-        import os
         self.reshard = os.environ.get("FTL_FSDP_RESHARD", "0") == "1"
         if self.reshard:   # two bucket-sized slots, by bucket parity
             self.stage = [torch.zeros(max_bucket, dtype=torch.bfloat16, device=self.device) for _ in range(2)]
@@ -178,7 +177,6 @@ class FsdpTrainer(PipelinedTrainer):
 
     def _finish_pipeline_state(self, flat: FlatState) -> None:
         """The part of PipelinedTrainer._make_flat_state that does not allocate parameter buffers."""
-        import os
         self.ranges = self._owned_ranges(flat)
         NB = len(self.buckets)
         self.parts = N.dp_partials(self.RS_CTAS)
