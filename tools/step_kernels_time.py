@@ -13,13 +13,14 @@ p = argparse.ArgumentParser()
 p.add_argument("--steps", type=int, default=3)
 p.add_argument("--seq", type=int, default=2048)
 p.add_argument("--layers", type=int, default=0)
+p.add_argument("--parallel", default="auto")
 a = p.parse_args()
 env = init_dist("cuda")
 cfg = ModelConfig(seq_len=a.seq, vocab_size=131072)
 if a.layers:
     cfg.n_layers = a.layers
 trainer = make_trainer(cfg, env, dtype=torch.bfloat16, lr=5e-5, warmup_steps=100, grad_max_norm=1.0, clip_mode="clip", seed=0,
-                       parallel="auto")
+                       parallel=a.parallel)
 g = torch.Generator().manual_seed(0)
 batches = [(torch.randint(0, cfg.vocab_size, (1, a.seq), generator=g).pin_memory(),
             torch.randint(0, cfg.vocab_size, (1, a.seq), generator=g).pin_memory()) for _ in range(2)]
@@ -34,9 +35,13 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
         last = trainer.step(*batches[i % 2])
     e1.record()
     torch.cuda.synchronize()
+if not env.is_main:   # every rank profiles (so that no rank runs ahead); rank 0 reports
+    env.barrier()
+    sys.exit(0)
+env.barrier()
 rows = [(e.key, e.device_time_total / a.steps / 1e3, e.count // a.steps) for e in prof.key_averages() if e.device_time_total > 0]
 total = sum(r[1] for r in rows)
-print(f"# Kernel time per training step (profiled under CUPTI, {a.steps} steps, seq {a.seq}): step {e0.elapsed_time(e1) / a.steps:.2f} ms, "
+print(f"# Kernel time per training step on rank 0 of {env.world_size} ({trainer.parallel}; profiled under CUPTI, {a.steps} steps, seq {a.seq}): step {e0.elapsed_time(e1) / a.steps:.2f} ms, "
       f"sum of kernel durations {total:.2f} ms\n")
 print("| ms / step | launches | share | kernel |\n|---:|---:|---:|---|")
 for k, t, n in sorted(rows, key=lambda r: -r[1])[:32]:
