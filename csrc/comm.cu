@@ -183,12 +183,26 @@ __global__ void __launch_bounds__(512)
 fsdp_gather_kernel(const __nv_bfloat16* const* __restrict__ peer_shards, int64_t off, __nv_bfloat16* __restrict__ dst,
                    int64_t nvec, int rank, const uint32_t* __restrict__ status) {
     if (*status != 0) return;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec * W; i += (int64_t)gridDim.x * blockDim.x) {
-        const int rr = (int)(i / nvec);
-        const int r = (rr + rank) % W;                     // start with the own shard, peers rotate
-        const int64_t k = i - (int64_t)rr * nvec;
-        const int4 v = ld_peer16(peer_shards[r] + off + k * 8);
-        *reinterpret_cast<int4*>(dst + ((int64_t)r * nvec + k) * 8) = v;
+    // four independent peer loads in flight per thread (NVLink round trips are ~3 us: bytes in flight are what set the rate)
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, total = nvec * W;
+    for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < total; i0 += 4 * stride) {
+        int4 v[4];
+        int64_t d[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t i = i0 + u * stride;
+            d[u] = -1;
+            if (i < total) {
+                const int rr = (int)(i / nvec);
+                const int r = (rr + rank) % W;                     // start with the own shard, peers rotate
+                const int64_t k = i - (int64_t)rr * nvec;
+                v[u] = ld_peer16(peer_shards[r] + off + k * 8);
+                d[u] = ((int64_t)r * nvec + k) * 8;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (d[u] >= 0) *reinterpret_cast<int4*>(dst + d[u]) = v[u];
     }
 }
 

@@ -100,17 +100,29 @@ __device__ __forceinline__ bool gather_one_item(const GemmArgs& g, int lane) {
     const int4* src = reinterpret_cast<const int4*>(g.gather_src[owner] + g.gather_off[mat] + row_in_shard * g.K);
     int4* dst = reinterpret_cast<int4*>(g.gather_dst[mat] + ((int64_t)hb * 128 + slice * kGatherSliceRows) * g.K);
     const int nvec = kGatherSliceRows * g.K / 8;
-    int i = lane;
-    for (; i + 7 * 32 < nvec; i += 8 * 32) {   // 8 independent 16-byte peer loads in flight per lane
-        int4 v[8];
+    int i = 0;
+    // 8 independent 32-byte peer loads in flight per lane: 8 KB per warp.  NVLink needs ~770 GB/s x ~3 us of round trip
+    // = 2.3 MB in flight per GPU just to stay busy; with 16-byte loads the ~600 gathering warps of a launch held 2.4 MB
+    // and the fused gather ran at ~280 GB/s.  (Rows are 16-byte aligned by contract; 32-byte accesses need K % 16 == 0
+    // and 32-byte aligned bases, otherwise the 16-byte loop below does all of it.)
+    if ((g.K & 15) == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 31) == 0) {
+        const int n32 = nvec / 2;
+        for (int k = lane; k + 7 * 32 < n32; k += 8 * 32) {
+            uint32_t v[8][8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
-            asm volatile("ld.global.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + i + u * 32));
+            for (int u = 0; u < 8; ++u)
+                asm volatile("ld.global.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                             : "=r"(v[u][0]), "=r"(v[u][1]), "=r"(v[u][2]), "=r"(v[u][3]), "=r"(v[u][4]), "=r"(v[u][5]),
+                               "=r"(v[u][6]), "=r"(v[u][7]) : "l"(src + 2 * (k + u * 32)));
 #pragma unroll
-        for (int u = 0; u < 8; ++u) dst[i + u * 32] = v[u];
+            for (int u = 0; u < 8; ++u)
+                asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                             :: "l"(dst + 2 * (k + u * 32)), "r"(v[u][0]), "r"(v[u][1]), "r"(v[u][2]), "r"(v[u][3]), "r"(v[u][4]),
+                                "r"(v[u][5]), "r"(v[u][6]), "r"(v[u][7]) : "memory");
+        }
+        i = (n32 / (8 * 32)) * (8 * 32) * 2;     // 16-byte vectors already moved
     }
-    for (; i < nvec; i += 32) dst[i] = src[i];
+    for (i += lane; i < nvec; i += 32) dst[i] = src[i];
     __threadfence();                           // the slice is visible device-wide before it is counted
     __syncwarp();
     if (lane == 0) atomicAdd(g.gather_done + mat * halves + hb, 1);
