@@ -119,7 +119,7 @@ __global__ void publish_kernel(const float* __restrict__ partial, int nparts, co
 
 __global__ void dp_finalize_kernel(const float* __restrict__ slots, int world, const float* __restrict__ hyper,
                                    float* __restrict__ stats, float* __restrict__ loss_out, int clip,
-                                   uint32_t* __restrict__ status) {
+                                   uint32_t* __restrict__ status, float* __restrict__ result) {
     if (threadIdx.x != 0) return;
     float total = 0.f, loss = 0.f;
     for (int r = 0; r < world; ++r) {   // same order on every rank -> bitwise-identical norm everywhere
@@ -135,6 +135,11 @@ __global__ void dp_finalize_kernel(const float* __restrict__ slots, int world, c
     // every rank folds the same slots in the same order, so all of them gate the same step (reference: the step that
     // meets a non-finite norm raises before optimizer.step(), utils.py:61, train.py:104-107)
     if (!finite && status) atomicMax(status, 3u);
+    // the step's whole report in one place, so that the host needs ONE device-to-host copy and no packing kernels
+    if (result) {
+        result[0] = loss; result[1] = norm; result[2] = coef; result[3] = finite ? 1.f : 0.f;
+        result[4] = status ? (float)*status : 0.f;
+    }
 }
 
 template <int W>
@@ -307,8 +312,8 @@ FTL_API int ftl_dp_publish(const float* partial, int nparts, const float* loss_l
 }
 
 FTL_API int ftl_dp_finalize(const float* slots, int world, const float* hyper, float* stats, float* loss_out, int clip,
-                            void* status, cudaStream_t stream) {
-    dp_finalize_kernel<<<1, 32, 0, stream>>>(slots, world, hyper, stats, loss_out, clip, (uint32_t*)status);
+                            void* status, float* result, cudaStream_t stream) {
+    dp_finalize_kernel<<<1, 32, 0, stream>>>(slots, world, hyper, stats, loss_out, clip, (uint32_t*)status, result);
     FTL_LAUNCH_CHECK();
     return 0;
 }

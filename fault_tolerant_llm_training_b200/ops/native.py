@@ -72,7 +72,7 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_dp_partials", [I])
     _sig(L, "ftl_dp_reduce_scatter", [P, I, I, I64, I64, P, P, I, P])
     _sig(L, "ftl_dp_publish", [P, I, P, P, I, I, P])
-    _sig(L, "ftl_dp_finalize", [P, I, P, P, P, I, P, P])
+    _sig(L, "ftl_dp_finalize", [P, I, P, P, P, I, P, P, P])
     _sig(L, "ftl_dp_adamw_allgather", [P, P, P, P, I, I, I64, I64, P, P, P, P, I, P])
     _sig(L, "ftl_ckpt_init", [I64])
     _sig(L, "ftl_ckpt_write", [ctypes.c_char_p, I, P, P, P, I, I, P])
@@ -360,10 +360,11 @@ def dp_publish(partial, nparts, loss_local, peer_slots, rank, world):
            "ftl_dp_publish")
 
 
-def dp_finalize(slots, world, hyper, stats, loss_out, clip=True, status=None):
-    """status (optional): the sticky comm status word; a non-finite norm sets it to 3 so that no later update runs."""
+def dp_finalize(slots, world, hyper, stats, loss_out, clip=True, status=None, result=None):
+    """status (optional): the sticky comm status word; a non-finite norm sets it to 3 so that no later update runs.
+    result (optional): fp32[>=5] receiving loss, norm, clip coefficient, finite flag, status — the step's report."""
     _check(lib().ftl_dp_finalize(_ptr(slots), world, _ptr(hyper), _ptr(stats), _ptr(loss_out), int(clip), _ptr(status),
-                                 _stream()), "ftl_dp_finalize")
+                                 _ptr(result), _stream()), "ftl_dp_finalize")
 
 
 def dp_adamw_allgather(peer_p, g, m, v, rank, world, lo, n, hyper, stats, status, commits=None, max_ctas=0):

@@ -147,7 +147,8 @@ class PipelinedTrainer(NativeTrainer):
             parts = self.engine.norm_arena if getattr(self, "fused_norm", False) else self.rs_partials
             N.dp_publish(parts, parts.numel(), loss, self.symm.table("slots"), env.rank, W)
             self._barrier()          # all slots written; nobody still reads my gradients for phase 1
-            N.dp_finalize(self.slots, W, hyper, self.stats, loss, clip=(self.clip_mode == "clip"), status=self.comm_status)
+            N.dp_finalize(self.slots, W, hyper, self.stats, loss, clip=(self.clip_mode == "clip"), status=self.comm_status,
+                          result=self.result_dev)
             self._result_handle = self._publish_result_on_comm(loss)
             for b in range(len(self.buckets)):
                 self._update_bucket(b, hyper)
@@ -173,10 +174,7 @@ class PipelinedTrainer(NativeTrainer):
         pass
 
     def _publish_result_on_comm(self, loss: torch.Tensor) -> LossHandle:
-        slot = self._result_slot
-        self.result_dev[0:1].copy_(loss)
-        self.result_dev[1:4].copy_(self.stats[0:3])
-        self.result_dev[4:5].copy_(self.comm_status.to(torch.float32))
+        slot = self._result_slot       # result_dev was filled by the finalize kernel: one D2H copy, no packing kernels
         self.result_host[slot].copy_(self.result_dev, non_blocking=True)
         self.events[slot].record()
         return LossHandle(self.result_host[slot], self.events[slot])

@@ -178,7 +178,9 @@ int ftl_dp_reduce_scatter(void* const* peer_g, int rank, int world, int64_t lo, 
 int ftl_dp_publish(const float* partial, int nparts, const float* loss_local, void* const* peer_slots, int rank,
                    int world, ftl_stream_t stream);
 int ftl_dp_finalize(const float* slots, int world, const float* hyper, float* stats, float* loss_out, int clip,
-                    void* status /* may be NULL; set to 3 when the norm is not finite */, ftl_stream_t stream);
+                    void* status /* may be NULL; set to 3 when the norm is not finite */,
+                    float* result /* may be NULL; fp32[5] = loss, norm, clip coefficient, finite, status */,
+                    ftl_stream_t stream);
 /* clip + AdamW on parameter range [lo, lo+n) with every updated vector stored to all ranks' copies (all-gather fused) */
 int ftl_dp_adamw_allgather(void* const* peer_p, const void* g, void* m, void* v, int rank, int world, int64_t lo,
                            int64_t n, const float* hyper, const float* stats, const void* status, void* commits,
