@@ -81,7 +81,7 @@ constexpr int kGatherSliceRows = 16, kGatherSlices = 128 / kGatherSliceRows;
 // The gather variants launch 4 more warps per CTA that do nothing but move weight slices: the epilogue warps alone only
 // gather while they wait for an accumulator, and with a heavy epilogue (SwiGLU: three stores per element) they are
 // rarely idle — the transfer then ran after the math instead of under it (0.498 ms fused vs 0.326 ms + 0.153 ms apart).
-constexpr int kGatherWarps = 4, kGemmThreadsGather = kGemmThreads + 32 * kGatherWarps;
+constexpr int kGatherWarpsMax = 8, kGemmThreadsGather = kGemmThreads + 32 * kGatherWarpsMax;
 
 // Copy one work item (kGatherSliceRows rows of B) from its owner to the local staging matrix.  One warp per item.
 __device__ __forceinline__ bool gather_one_item(const GemmArgs& g, int lane) {
@@ -678,6 +678,17 @@ static int launch_c(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMa
     return (int)cudaLaunchKernelEx(&cfg, kern, a, b, a2, b2, g);
 }
 
+// dedicated gather warps per CTA in the fused all-gather launches (FTL_GATHER_WARPS = 0..8, default 4)
+static int gather_warps() {
+    static int w = -1;
+    if (w < 0) {
+        const char* e = getenv("FTL_GATHER_WARPS");
+        w = e ? atoi(e) : 4;
+        if (w < 0 || w > kGatherWarpsMax) w = 4;
+    }
+    return w;
+}
+
 template <int kEpi, bool kAMn, bool kBMn>
 static int launch_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& a2, const CUtensorMap& b2,
                        const GemmArgs& g, int max_ctas, cudaStream_t stream) {
@@ -695,7 +706,7 @@ static int launch_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
     if (grid < 2) grid = 2;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(g.gather_src ? kGemmThreadsGather : kGemmThreads);
+    cfg.blockDim = dim3(g.gather_src ? kGemmThreads + 32 * gather_warps() : kGemmThreads);
     cfg.dynamicSmemBytes = kSmemBytes2;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];

@@ -125,11 +125,15 @@ def main():
         act, gate, up = (torch.empty(T, F, dtype=torch.bfloat16, device=dev) for _ in range(3))
         scratch = torch.zeros(1 + 2 * (F // 128) + 8, dtype=torch.int32, device=dev)
         ms_f = timed(lambda: N.gemm_swiglu_gather(x, w1, w3, act, gate, up, wsh.table("own"), 0, (F // W) * d, F // W, r, W, scratch))
+        # the same launch with every "owner" pointing at this rank's own shard: the mechanism without NVLink
+        local_tab = torch.tensor([wsh.local_ptr["own"]] * W, dtype=torch.int64, device=dev)
+        ms_loc = timed(lambda: N.gemm_swiglu_gather(x, w1, w3, act, gate, up, local_tab, 0, (F // W) * d, F // W, r, W, scratch))
         ms_l = timed(lambda: N.gemm_swiglu(x, w1, w3, act, gate, up))
         fl = 2.0 * T * d * 2 * F
         nv = (W - 1) * 2 * (F // W) * d * 2
         report(f"gemm_swiglu_gather (all-gather fused into the gate|up GEMM, W={W})", ms_f, nv, 2 * F * d * 2 * 2 + 3 * T * F * 2, fl,
-               note=f"same GEMM on local weights: {ms_l:.3f} ms; a separate gather of these weights would add "
+               note=f"same GEMM on local weights: {ms_l:.3f} ms; fused gather with all sources local: {ms_loc:.3f} ms; "
+                    f"FTL_GATHER_WARPS={os.environ.get('FTL_GATHER_WARPS', '4')}; a separate gather of these weights would add "
                     f"{nv / (NVLINK_GBS * 1e9) * 1e3:.3f} ms at 770 GB/s")
     env.shutdown()
 
