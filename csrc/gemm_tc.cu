@@ -77,7 +77,13 @@ struct GemmArgs {
     int* gather_done;                        // [nmat * N/128] slices finished per half block (zeroed before launch)
 };
 
-constexpr int kGatherSliceRows = 16, kGatherSlices = 128 / kGatherSliceRows;
+// Work items are SMALL (2 rows = 16 KB at K = 4096) on purpose.  All gathering warps of the GPU pull items off one
+// in-order dispenser and share the NVLink bandwidth equally, so everything that is in flight completes at about the
+// same time: with 16-row items ~1,200 warps held 150 MB in flight, whole waves of half blocks landed together and the
+// MMAs waited for the end of each wave (0.46 ms instead of 0.33 ms for the gate|up GEMM at W = 2, whatever the number
+// of gathering warps).  With 2-row items the window in flight is ~19 MB — the ~9 n-blocks the CTA pairs are working
+// on — and it slides over the weight matrix in the order the producers need it.
+constexpr int kGatherSliceRows = 2, kGatherSlices = 128 / kGatherSliceRows;
 // The gather variants launch 4 more warps per CTA that do nothing but move weight slices: the epilogue warps alone only
 // gather while they wait for an accumulator, and with a heavy epilogue (SwiGLU: three stores per element) they are
 // rarely idle — the transfer then ran after the math instead of under it (0.498 ms fused vs 0.326 ms + 0.153 ms apart).
