@@ -166,8 +166,25 @@ class BatchStream:
             examples = [self.dataset[first + j] for j in range(self.batch_size)]
             inputs, labels = self.collator(examples)
         if self.pin_memory:
-            inputs, labels = inputs.pin_memory(), labels.pin_memory()
+            inputs, labels = self._to_pinned(inputs, labels)
         return inputs, labels
+
+    def _to_pinned(self, inputs: torch.Tensor, labels: torch.Tensor):
+        """Copy into a small ring of page-locked buffers allocated once.  `tensor.pin_memory()` per batch is a
+        cudaHostAlloc on the producer thread every step: slow, and it takes driver locks the training thread needs for
+        its ~800 kernel launches.  The ring is deeper than the prefetch queue plus the batches a consumer can still be
+        reading (the trainers copy a batch out before they ask for the next one)."""
+        key = (tuple(inputs.shape), inputs.dtype, tuple(labels.shape), labels.dtype)
+        if getattr(self, "_pin_key", None) != key:
+            n = self._prefetch + 8
+            self._pin_ring = [(torch.empty(inputs.shape, dtype=inputs.dtype).pin_memory(),
+                               torch.empty(labels.shape, dtype=labels.dtype).pin_memory()) for _ in range(n)]
+            self._pin_key, self._pin_next = key, 0
+        a, b = self._pin_ring[self._pin_next]
+        self._pin_next = (self._pin_next + 1) % len(self._pin_ring)
+        a.copy_(inputs)
+        b.copy_(labels)
+        return a, b
 
     def _worker(self, start: int) -> None:
         i = start
@@ -185,6 +202,11 @@ class BatchStream:
             i += 1
 
     def _start(self) -> None:
+        # The producer tokenises in Python; with the default 5 ms GIL switch interval it can hold the interpreter for
+        # 5 ms at a time while the training thread is in the middle of its per-step launch sequence.
+        import sys
+        if sys.getswitchinterval() > 5e-4:
+            sys.setswitchinterval(5e-4)
         self._stop.clear()
         self._q = queue.Queue(maxsize=self._prefetch)
         self._thread = threading.Thread(target=self._worker, args=(self.batches_consumed,), daemon=True)
