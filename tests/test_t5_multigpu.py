@@ -126,3 +126,30 @@ def test_nvls_collectives_track_one_gpu(world):
     assert r.returncode == 0 and out and out[0]["ok"] and out[0]["ranks_identical"], r.stdout[-2000:] + r.stderr[-2000:]
     r, out = _torchrun(world, "tools/fsdp_check.py", env={"FTL_COLLECTIVE": "nvls"})
     assert r.returncode == 0 and out and out[0]["ok"], r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@needs2
+@pytest.mark.parametrize("mode", ["dp", "fsdp"])
+def test_two_rank_usr1_chain_is_bitwise(tmp_path, mode):
+    """Kill/resume on two ranks: SIGUSR1 to both -> same step boundary on both -> sharded checkpoint -> resubmit ->
+    resume; losses and the final model / optimizer / scheduler / data state are bitwise those of an uninterrupted
+    two-rank run (BASELINE.json config 5 in miniature, on the peer-load data plane)."""
+    import signal
+
+    from test_t2_fault_tolerance import _digest
+
+    mk = lambda steps, *more: TINY + ["--dataset", os.path.join(str(tmp_path), "d.parquet"), "--training-steps", str(steps),
+                                      "--parallel", mode] + list(more)
+    full = Job(tmp_path, 9000, mk(60, "--save-final"), nproc=2, timeout=600)
+    assert full.returncode == 0 and "Training completed" in full.text, full.text[-3000:]
+    j1 = Job(tmp_path, 9001, mk(60), nproc=2, signal_at=12, sig=signal.SIGUSR1, timeout=600)
+    assert j1.returncode == 0 and "[EXIT HANDLER] Job timed out, saving checkpoint." in j1.text, j1.text[-3000:]
+    assert j1.sbatch_calls == [f"{tmp_path}/train.sh 9001"]
+    j2 = Job(tmp_path, 9002, mk(60, "--save-final", "--checkpoint-id", "9001"), nproc=2, timeout=600)
+    assert j2.returncode == 0 and "Training completed" in j2.text, j2.text[-3000:]
+    merged = dict(j1.losses)
+    merged.update(j2.losses)
+    assert merged == full.losses
+    a = torch.load(full.ckpt_path(), weights_only=False)
+    b = torch.load(j2.ckpt_path(), weights_only=False)
+    assert _digest(a) == _digest(b)

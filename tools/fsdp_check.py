@@ -12,7 +12,7 @@ from fault_tolerant_llm_training_b200.config import ModelConfig  # noqa: E402
 from fault_tolerant_llm_training_b200.parallel.env import DistEnv, init_dist  # noqa: E402
 from fault_tolerant_llm_training_b200.trainer import make_trainer  # noqa: E402
 
-CFG = ModelConfig(dim=1024, n_layers=3, n_heads=8, n_kv_heads=4, multiple_of=256, seq_len=256, vocab_size=8192)
+CFG = ModelConfig(dim=1024, n_layers=3, n_heads=8, n_kv_heads=4, multiple_of=1024, seq_len=256, vocab_size=8192)  # ffn 3072: row shards of 128 at W = 2, 4, 8
 STEPS = 6
 
 
