@@ -243,6 +243,97 @@ adamw_shard_kernel(__nv_bfloat16* __restrict__ p, const __nv_bfloat16* __restric
     }
 }
 
+// ---- embedding bucket: sparse reduce-scatter --------------------------------------------------------------------------
+// The table gradient is 1 GB per rank of which only the rows of the step's tokens (<= T per rank) are non-zero, and it is
+// the LAST gradient of the backward: its dense reduce-scatter (every rank pulling W-1 shards of zeros, 1.5 ms at W = 8
+// after a 0.35 ms memset) sat between the end of one step and the first kernel of the next.  Here every rank first
+// publishes its token ids to all peers (emb_tokens_push_kernel, at the start of the backward); after the barrier the
+// owner of a row range reduces only the rows that occur in ANY rank's list: the CTA of the first occurrence of an id (in
+// rank-major, position-minor order) adds the rows of the ranks that hold the id, in rank order — bit-identical to the
+// dense fixed-order sum, since all other addends are +0 — and writes the bf16 total and a sum-of-squares partial.
+// CTAs [W*T, 2*W*T) clear the rows the PREVIOUS step's union wrote in this rank's range and this step's does not.
+// toks: [W][cap] int64 (this rank's copy of everybody's ids); [lo, hi): this rank's element range of the flat gradient.
+__global__ void emb_tokens_push_kernel(const int64_t* __restrict__ tokens, int64_t* const* __restrict__ peer_toks,
+                                       int64_t slot_off, int rank, int T, int cap) {
+    int64_t* dst = peer_toks[blockIdx.x] + slot_off + (int64_t)rank * cap;
+    for (int i = threadIdx.x; i < T; i += blockDim.x) dst[i] = tokens[i];
+    __threadfence_system();
+}
+
+template <int W>
+__global__ void __launch_bounds__(128)
+emb_sparse_reduce_kernel(__nv_bfloat16* const* __restrict__ peer_g, int rank, const int64_t* __restrict__ toks,
+                         const int64_t* __restrict__ toks_prev, int T, int cap, int64_t emb_off, int dim, int vocab,
+                         int64_t lo, int64_t hi, float* __restrict__ partial, const uint32_t* __restrict__ status) {
+    __shared__ float red[33];
+    const int tid = threadIdx.x;
+    const int WT = W * T;
+    const bool clearing = (int)blockIdx.x >= WT;
+    const int idx = clearing ? blockIdx.x - WT : blockIdx.x;
+    const int q = idx / T, t = idx - q * T;
+    if (*status != 0) {
+        if (!clearing && tid == 0) partial[idx] = 0.f;
+        return;
+    }
+    const int64_t* list = clearing ? toks_prev : toks;
+    const int64_t id = list[(int64_t)q * cap + t];
+    // this rank's part of the row
+    const int64_t r0 = emb_off + id * dim;
+    const int64_t e0 = r0 > lo ? r0 : lo, e1 = (r0 + dim) < hi ? (r0 + dim) : hi;
+    bool skip = id < 0 || id >= vocab || e0 >= e1;
+    // first occurrence in (rank, position) order?
+    if (!skip) {
+        for (int qq = 0; qq <= q; ++qq) {
+            const int n = qq < q ? T : t;
+            for (int j = tid; j < n; j += blockDim.x) skip |= list[(int64_t)qq * cap + j] == id;
+        }
+    }
+    if (clearing && !skip)   // rows of the current union are (over)written by their owner CTA below
+        for (int j = tid; j < WT; j += blockDim.x) skip |= toks[(int64_t)(j / T) * cap + (j % T)] == id;
+    if (__syncthreads_or(skip)) {
+        if (!clearing && tid == 0) partial[idx] = 0.f;
+        return;
+    }
+    __nv_bfloat16* mine = peer_g[rank];
+    const int64_t v0 = e0 >> 3, v1 = e1 >> 3;          // ranges are multiples of 8 elements
+    if (clearing) {
+        bf16x8 z;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) z.v[k] = __floats2bfloat162_rn(0.f, 0.f);
+        for (int64_t i = v0 + tid; i < v1; i += blockDim.x) st8(mine + i * 8, z);
+        return;
+    }
+    bool has[W];
+#pragma unroll
+    for (int qq = 0; qq < W; ++qq) {
+        bool h = false;
+        for (int j = tid; j < T; j += blockDim.x) h |= toks[(int64_t)qq * cap + j] == id;
+        has[qq] = __syncthreads_or(h);
+    }
+    float ss = 0.f;
+    for (int64_t i = v0 + tid; i < v1; i += blockDim.x) {
+        float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int qq = 0; qq < W; ++qq) {               // fixed order: rank 0, 1, ...
+            if (has[qq]) {
+                const int4 raw = ld_peer16(peer_g[qq] + i * 8);
+                float f[8];
+                unpack8(*reinterpret_cast<const bf16x8*>(&raw), f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) s[j] += f[j];
+            }
+        }
+        const bf16x8 o = pack8(s);
+        st8(mine + i * 8, o);
+        float f[8];
+        unpack8(o, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += f[j] * f[j];
+    }
+    const float total = block_sum(ss, red);
+    if (tid == 0) partial[idx] = total;
+}
+
 static inline int comm_grid(int64_t nvec, int max_ctas) {
     int64_t blocks = (nvec + 511) / 512;
     int64_t cap = max_ctas > 0 ? max_ctas : (int64_t)kNumSMs * 4;
@@ -300,6 +391,34 @@ FTL_API int ftl_dp_reduce_scatter(void* const* peer_g, int rank, int world, int6
     switch (world) { RS_CASE(1) RS_CASE(2) RS_CASE(3) RS_CASE(4) RS_CASE(5) RS_CASE(6) RS_CASE(7) RS_CASE(8)
         default: return (int)cudaErrorInvalidValue; }
 #undef RS_CASE
+    FTL_LAUNCH_CHECK();
+    return 0;
+}
+
+// Publish this rank's token ids of the step into slot `slot_off` (elements) of every peer's id buffer ([.][W][cap] int64).
+FTL_API int ftl_emb_tokens_push(const int64_t* tokens, void* const* peer_toks, int64_t slot_off, int rank, int world, int T,
+                                int cap, cudaStream_t stream) {
+    if (world < 1 || world > kMaxRanks || T <= 0 || T > cap) return (int)cudaErrorInvalidValue;
+    emb_tokens_push_kernel<<<world, 256, 0, stream>>>(tokens, (int64_t* const*)peer_toks, slot_off, rank, T, cap);
+    FTL_LAUNCH_CHECK();
+    return 0;
+}
+
+// Sparse reduce-scatter of the embedding-table gradient over this rank's element range [lo, hi) of the flat gradient
+// (see emb_sparse_reduce_kernel).  toks / toks_prev: this rank's [W][cap] id lists of this / the previous step (prev may
+// be NULL on the first step, when the range is still all zero).  partial: fp32 [world * T].
+FTL_API int ftl_emb_sparse_reduce(void* const* peer_g, int rank, int world, const int64_t* toks, const int64_t* toks_prev,
+                                  int T, int cap, int64_t emb_off, int dim, int vocab, int64_t lo, int64_t hi,
+                                  float* partial, const void* status, cudaStream_t stream) {
+    if (lo % 8 || hi % 8 || emb_off % 8 || dim % 8 || T <= 0 || T > cap || lo >= hi) return (int)cudaErrorInvalidValue;
+    const unsigned grid = (unsigned)((toks_prev ? 2 : 1) * world * T);
+    auto P = (__nv_bfloat16* const*)peer_g;
+    auto S = (const uint32_t*)status;
+#define ESR_CASE(W) case W: emb_sparse_reduce_kernel<W><<<grid, 128, 0, stream>>>(P, rank, toks, toks_prev, T, cap, emb_off, \
+        dim, vocab, lo, hi, partial, S); break;
+    switch (world) { ESR_CASE(1) ESR_CASE(2) ESR_CASE(3) ESR_CASE(4) ESR_CASE(5) ESR_CASE(6) ESR_CASE(7) ESR_CASE(8)
+        default: return (int)cudaErrorInvalidValue; }
+#undef ESR_CASE
     FTL_LAUNCH_CHECK();
     return 0;
 }

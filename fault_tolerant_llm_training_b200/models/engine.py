@@ -262,6 +262,7 @@ class NativeEngine:
         self.norm_arena: Optional[torch.Tensor] = None
         self._arena_off = 0
         self.hook_params_bwd = None   # called before the backward of bucket b reads its parameters
+        self.hook_tokens = None       # called at the start of the backward with the step's flat token ids
         self.fused_gather = None      # FSDP: object with qkv(i, x, out) / swiglu(i, x, act, gate, up) running the
                                       # gather-fused GEMMs for layer i (parallel/fsdp.py)
 
@@ -417,6 +418,8 @@ class NativeEngine:
         L = c.n_layers
         dl = self.logits
         self._arena_off = 0
+        if self.hook_tokens is not None:
+            self.hook_tokens(tokens.view(-1))
         _Nvtx.push("backward")
         _Nvtx.push("bwd head")
         if self.hook_params_bwd is not None:

@@ -104,6 +104,8 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_mc_bind_map", [ctypes.c_uint64, ctypes.c_uint64, I64, PP])
     _sig(L, "ftl_nvls_reduce_scatter", [P, P, I64, I64, P, P, I, P])
     _sig(L, "ftl_nvls_adamw_allgather", [P, P, P, P, P, I64, I64, P, P, P, P, I, P])
+    _sig(L, "ftl_emb_tokens_push", [P, P, I64, I, I, I, I, P])
+    _sig(L, "ftl_emb_sparse_reduce", [P, I, I, P, P, I, I, I64, I, I, I64, I64, P, P, P])
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -353,6 +355,20 @@ def dp_partials(max_ctas=0) -> int:
 def dp_reduce_scatter(peer_g, rank, world, lo, n, partial, status, max_ctas=0):
     _check(lib().ftl_dp_reduce_scatter(_ptr(peer_g), rank, world, lo, n, _ptr(partial), _ptr(status), max_ctas, _stream()),
            "ftl_dp_reduce_scatter")
+
+
+def emb_tokens_push(tokens, peer_toks, slot_off, rank, world, cap):
+    """Store this rank's token ids of the step into every peer's id buffer (slot_off in elements)."""
+    assert tokens.dtype == torch.int64 and tokens.is_contiguous()
+    _check(lib().ftl_emb_tokens_push(_ptr(tokens), _ptr(peer_toks), slot_off, rank, world, tokens.numel(), cap, _stream()),
+           "ftl_emb_tokens_push")
+
+
+def emb_sparse_reduce(peer_g, rank, world, toks, toks_prev, T, cap, emb_off, dim, vocab, lo, hi, partial, status):
+    """Reduce-scatter of the embedding-table gradient restricted to the rows that occur in any rank's token list."""
+    assert partial.dtype == torch.float32 and partial.numel() >= world * T
+    _check(lib().ftl_emb_sparse_reduce(_ptr(peer_g), rank, world, _ptr(toks), _ptr(toks_prev), T, cap, emb_off, dim, vocab,
+                                       lo, hi, _ptr(partial), _ptr(status), _stream()), "ftl_emb_sparse_reduce")
 
 
 def dp_publish(partial, nparts, loss_local, peer_slots, rank, world):

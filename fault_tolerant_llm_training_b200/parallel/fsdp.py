@@ -123,8 +123,8 @@ class FsdpTrainer(PipelinedTrainer):
         flag_words = N.lib().ftl_comm_flag_words()
         # fully-sharded mode has no parameter broadcast; its gradient reduce-scatter can go through the switch too
         self.nvls = os.environ.get("FTL_COLLECTIVE", "p2p") == "nvls" and W > 1
-        self.symm = make_symmetric(env, {"own": self.own_numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64},
-                                   multicast=("g",) if self.nvls else ())
+        self.symm = make_symmetric(env, dict({"own": self.own_numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64},
+                                             **self._tok_buffers()), multicast=("g",) if self.nvls else ())
         self.p_own = self.symm.tensor("own", torch.bfloat16)
         self.m_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
         self.v_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)

@@ -36,6 +36,10 @@ class PipelinedTrainer(NativeTrainer):
     # The embedding bucket's gradients are the last ones of the backward: nothing else runs while its phase 1 (1 GB at
     # W = 1) delays the norm, the first AdamW launch and with them the next forward, so it gets the whole GPU.
     RS_LAST_CTAS = int(os.environ.get("FTL_RS_LAST_CTAS", "0"))
+    # W > 1: the embedding bucket (the last gradient of the backward, 1 GB of mostly zeros) is reduced row-sparsely: the
+    # ranks exchange their token ids and only rows that occur in some rank's batch cross NVLink (csrc/comm.cu).
+    SPARSE_EMB = os.environ.get("FTL_SPARSE_EMB_RS", "1") != "0"
+    TOK_CAP = 65536          # token ids per rank and step the id exchange buffer holds
 
     # ---- state ---------------------------------------------------------------------------------------------------
     def _make_flat_state(self) -> FlatState:
@@ -48,8 +52,8 @@ class PipelinedTrainer(NativeTrainer):
         # need.  FTL_COLLECTIVE=nvls: the reduction and the broadcast are done by the NVSwitch (multimem instructions on
         # a multicast mapping of p and g); fewer NVLink bytes, summation order up to the switch.
         self.nvls = os.environ.get("FTL_COLLECTIVE", "p2p") == "nvls" and W > 1
-        self.symm = make_symmetric(env, {"p": numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64},
-                                   multicast=("p", "g") if self.nvls else ())
+        self.symm = make_symmetric(env, dict({"p": numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64},
+                                             **self._tok_buffers()), multicast=("p", "g") if self.nvls else ())
         bufs = {"p": lambda n: self.symm.tensor("p", torch.bfloat16), "g": lambda n: self.symm.tensor("g", torch.bfloat16)}
         flat = FlatState(self.model, self.device, buffers=bufs, pad_to=1024)
         assert flat.numel == numel
@@ -81,6 +85,11 @@ class PipelinedTrainer(NativeTrainer):
         self._hyper = None
         return flat
 
+    def _tok_buffers(self) -> dict:
+        """Peer-mapped buffer for the token-id exchange of the sparse embedding reduce: 3 step slots x W ranks x TOK_CAP."""
+        W = self.env.world_size
+        return {"toks": 3 * W * self.TOK_CAP * 8} if (W > 1 and self.SPARSE_EMB) else {}
+
     def _owned_ranges(self, flat: FlatState) -> List[List[Tuple[int, int]]]:
         """Data parallel: every bucket is cut into W equal contiguous sub-shards; rank r owns the r-th."""
         W, r, out = self.env.world_size, self.env.rank, []
@@ -101,6 +110,19 @@ class PipelinedTrainer(NativeTrainer):
         if fresh:
             self.engine.hook_params = self._wait_params
             self.engine.hook_grads = self._grads_done
+            W, T = self.env.world_size, B * S
+            self.sparse_emb = (W > 1 and self.SPARSE_EMB and T <= self.TOK_CAP and len(self.ranges[0]) == 1
+                               and "toks" in self.symm.sizes)
+            if self.sparse_emb:
+                self.engine.hook_tokens = self._push_tokens
+                self.engine.sparse_emb_zero = True       # the backward clears only its own previous rows: no 1 GB memset
+                self.engine.g_emb.zero_()                # once: from here on every row outside the token lists stays zero
+                self.toks_local = self.symm.tensor("toks", torch.int64)
+                self._tok_step, self._have_prev = 0, False
+                k = sum(len(rs) for rs in self.ranges)
+                self.rs_partials = torch.zeros(max(k, 1) * self.parts + W * T, dtype=torch.float32, device=self.device)
+                torch.cuda.synchronize()
+                self.env.barrier()
             # One rank has nothing to reduce: the kernels that write the gradients also emit the norm partials, and
             # phase 1 (a 16 GB re-read of the gradient buffer at W = 1) disappears.
             self.fused_norm = (type(self) is PipelinedTrainer and self.env.world_size == 1
@@ -125,6 +147,9 @@ class PipelinedTrainer(NativeTrainer):
             if getattr(self, "fused_norm", False):
                 return
             self._barrier()          # every rank's bucket-b gradients are complete
+            if b == 0 and getattr(self, "sparse_emb", False):
+                self._reduce_embedding_sparse()
+                return
             for (a, e), k in zip(self.ranges[b], self.range_slot[b]):
                 part = self.rs_partials[k * self.parts:(k + 1) * self.parts]
                 ctas = self.RS_LAST_CTAS if b == 0 else self.RS_CTAS
@@ -133,6 +158,25 @@ class PipelinedTrainer(NativeTrainer):
                 else:
                     N.dp_reduce_scatter(self.symm.table("g"), self.env.rank, self.env.world_size, a, e - a, part,
                                         self.comm_status, max_ctas=ctas)
+
+    def _push_tokens(self, flat_tok: torch.Tensor) -> None:
+        """Start of the backward (compute stream): hand this step's token ids to every peer."""
+        W, cap = self.env.world_size, self.TOK_CAP
+        self._tok_slot = self._tok_step % 3
+        N.emb_tokens_push(flat_tok, self.symm.table("toks"), self._tok_slot * W * cap, self.env.rank, W, cap)
+
+    def _reduce_embedding_sparse(self) -> None:
+        """Comm stream, after the barrier that follows the embedding backward on every rank."""
+        W, cap, e = self.env.world_size, self.TOK_CAP, self.engine
+        cur = self.toks_local[self._tok_slot * W * cap:]
+        prev = self.toks_local[((self._tok_step - 1) % 3) * W * cap:] if self._have_prev else None
+        (a, hi), = self.ranges[0]
+        emb_off = self.flat.index["tok_embeddings.weight"][0]
+        tail = self.rs_partials[self.rs_partials.numel() - W * e.T:]
+        N.emb_sparse_reduce(self.symm.table("g"), self.env.rank, W, cur, prev, e.T, cap, emb_off, self.cfg.dim,
+                            self.cfg.vocab_size, a, hi, tail, self.comm_status)
+        self._tok_step += 1
+        self._have_prev = True
 
     # ---- step pieces ---------------------------------------------------------------------------------------------
     def _begin_step(self, hyper: torch.Tensor) -> None:

@@ -170,6 +170,14 @@ int ftl_comm_flag_words(void);                                  /* uint32 words 
 int ftl_barrier(void* const* peer_flags, int rank, int world, uint32_t epoch, void* status, int64_t timeout_ms,
                 ftl_stream_t stream);
 int ftl_raise_abort(void* const* peer_flags, int world, ftl_stream_t stream);
+/* Embedding-table gradient: publish this rank's token ids to all peers, then reduce only the rows that occur in any
+ * rank's list over this rank's element range [lo, hi) of the flat gradient (bit-identical to the dense fixed-order sum;
+ * rows of the previous step's lists that are not rewritten are cleared).  No counterpart in the reference. */
+int ftl_emb_tokens_push(const int64_t* tokens, void* const* peer_toks, int64_t slot_off, int rank, int world, int T,
+                        int cap, ftl_stream_t stream);
+int ftl_emb_sparse_reduce(void* const* peer_g, int rank, int world, const int64_t* toks, const int64_t* toks_prev, int T,
+                          int cap, int64_t emb_off, int dim, int vocab, int64_t lo, int64_t hi, float* partial,
+                          const void* status, ftl_stream_t stream);
 int ftl_dp_partials(int max_ctas);                              /* floats of `partial` one reduce-scatter launch writes */
 /* gradient range [lo, lo+n) of every rank summed in rank order into this rank's buffer, with the sum of squares of the
  * result in `partial` (reduce-scatter fused with the norm) */

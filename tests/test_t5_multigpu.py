@@ -98,6 +98,7 @@ def test_comm_stress_barrier_timeout_and_delays():
     res = out[-1]
     assert res["barrier_epochs_ok"] and res["gather_gemm_ok"] and res["timeout_status"] == 1 and res["untouched_after_timeout"], res
     assert res["abort_status"] == 2, res
+    assert res["sparse_embedding_reduce_ok"], res
 
 
 def _multicast_ok() -> bool:

@@ -7,7 +7,9 @@
      delays in front, result compared bit for bit with the same GEMM on a locally assembled weight;
   3. the barrier's time budget: one rank stays away -> the others come back with status 1, and an update launched with
      that status leaves parameters and moments untouched;
-  4. the abort word: one rank raises it while the others wait -> status 2.
+  4. the abort word: one rank raises it while the others wait -> status 2;
+  5. the row-sparse reduce-scatter of the embedding gradient against the dense fixed-order one: bit-equal shards over
+     three steps with changing token lists (rows of earlier steps must end up zero again).
 
     python -m torch.distributed.run --nproc-per-node W --master-addr 127.0.0.1 tools/comm_stress.py
 """
@@ -121,8 +123,45 @@ def main():
         N.raise_abort(symm.table("flags3"), W)
     torch.cuda.synchronize()
     abort_status = int(st3.item())
+    # ---- 5. sparse vs dense embedding reduce-scatter ----------------------------------------------------------------
+    V, D, Tn, cap = 4096, 256, 512, 1024
+    es = SymmetricBuffers(env, {"gA": V * D * 2, "gB": V * D * 2, "toks": 3 * W * cap * 8, "fl": flag_words * 4})
+    gA, gB = es.tensor("gA", torch.bfloat16).view(V, D), es.tensor("gB", torch.bfloat16).view(V, D)
+    toks = es.tensor("toks", torch.int64)
+    st5 = torch.zeros(1, dtype=torch.int32, device=dev)
+    rows = V // W
+    lo, hi = r * rows * D, (r + 1) * rows * D
+    partsA = torch.zeros(N.dp_partials(0), device=dev)
+    partsB = torch.zeros(W * Tn, device=dev)
+    sparse_ok, ep, prev_tok = True, 0, None
+    for step in range(3):
+        g5 = torch.Generator().manual_seed(900 + 10 * step + r)
+        tok = torch.randint(0, V, (Tn,), generator=g5)
+        tok[::5] = int(tok[0])                              # repeats inside a rank
+        tok[1::7] = (step * 37) % V                         # an id every rank shares
+        tok = tok.to(dev)
+        dout = (torch.randn(Tn, D, generator=g5) * 0.3).to(dev, torch.bfloat16)
+        gA.zero_()
+        N.embedding_bwd_direct(tok, None, dout, gA)
+        N.embedding_bwd_direct(tok, prev_tok, dout, gB)     # gB is never memset: only the previous rows are cleared
+        slot = step % 3
+        N.emb_tokens_push(tok, es.table("toks"), slot * W * cap, r, W, cap)
+        ep += 1
+        N.barrier(es.table("fl"), r, W, ep, st5, 20000)
+        N.dp_reduce_scatter(es.table("gA"), r, W, lo, hi - lo, partsA, st5)
+        cur = toks[slot * W * cap:]
+        prv = toks[((step - 1) % 3) * W * cap:] if step else None
+        N.emb_sparse_reduce(es.table("gB"), r, W, cur, prv, Tn, cap, 0, D, V, lo, hi, partsB, st5)
+        torch.cuda.synchronize()
+        a, b = gA.view(-1)[lo:hi], gB.view(-1)[lo:hi]
+        sparse_ok &= bool(torch.equal(a, b))
+        sparse_ok &= bool(torch.allclose(partsA.sum(), partsB.sum(), rtol=1e-4, atol=1e-4))
+        ep += 1
+        N.barrier(es.table("fl"), r, W, ep, st5, 20000)      # peers have finished reading my rows before the next step
+        torch.cuda.synchronize()
+        prev_tok = tok
     res = env.gather_objects({"barrier_ok": barrier_ok, "gemm_ok": gemm_ok, "timeout": timeout_status,
-                              "untouched": untouched, "abort": abort_status})
+                              "untouched": untouched, "abort": abort_status, "sparse_ok": sparse_ok})
     if r == 0:
         others = res[1:]
         print(json.dumps({"world": W, "epochs": a.epochs, "barrier_s": round(barrier_s, 2),
@@ -130,7 +169,8 @@ def main():
                           "gather_gemm_ok": all(x["gemm_ok"] for x in res), "gemms": a.gemms,
                           "timeout_status": max(x["timeout"] for x in others),
                           "untouched_after_timeout": all(x["untouched"] for x in res),
-                          "abort_status": min(x["abort"] for x in others)}), flush=True)
+                          "abort_status": min(x["abort"] for x in others),
+                          "sparse_embedding_reduce_ok": all(x["sparse_ok"] for x in res)}), flush=True)
     env.shutdown()
 
 
