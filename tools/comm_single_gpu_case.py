@@ -15,7 +15,14 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from fault_tolerant_llm_training_b200.ops import native as N  # noqa: E402
 
 
+ONCE = "--once" in sys.argv      # under ncu: one launch per kernel
+
+
 def timed(fn, n=5):
+    if ONCE:
+        fn()
+        torch.cuda.synchronize()
+        return 0.0
     for _ in range(2):
         fn()
     ts = []
