@@ -153,8 +153,8 @@ def main():
         prv = toks[((step - 1) % 3) * W * cap:] if step else None
         N.emb_sparse_reduce(es.table("gB"), r, W, cur, prv, Tn, cap, 0, D, V, lo, hi, partsB, st5)
         torch.cuda.synchronize()
-        a, b = gA.view(-1)[lo:hi], gB.view(-1)[lo:hi]
-        sparse_ok &= bool(torch.equal(a, b))
+        dense_shard, sparse_shard = gA.view(-1)[lo:hi], gB.view(-1)[lo:hi]
+        sparse_ok &= bool(torch.equal(dense_shard, sparse_shard))
         sparse_ok &= bool(torch.allclose(partsA.sum(), partsB.sum(), rtol=1e-4, atol=1e-4))
         ep += 1
         N.barrier(es.table("fl"), r, W, ep, st5, 20000)      # peers have finished reading my rows before the next step
