@@ -86,3 +86,46 @@ def test_batch_stream_resume_and_rank_sharding(tmp_path):
     assert torch.equal(next(ff)[0], want[0])
     for s in [one, fresh, ff] + ranks:
         s.close()
+
+
+def test_batchstream_restore_validates_geometry(tmp_path):
+    """Resume with another world size / batch size (ADVICE r1): padded mode converts the position exactly or refuses;
+    packed mode refuses; the same geometry takes this rank's own state."""
+    import pytest as _pytest
+
+    from fault_tolerant_llm_training_b200.data.datasets import BatchStream, CollatorForCLM, ParquetDataset
+    from fault_tolerant_llm_training_b200.data.synthetic import write_synthetic_parquet
+    from fault_tolerant_llm_training_b200.data.tokenizer import OfflineTokenizer
+
+    path = str(tmp_path / "d.parquet")
+    write_synthetic_parquet(path, num_docs=64, min_len=40, max_len=80, vocab_size=512)
+    tok = OfflineTokenizer(512)
+    mk = lambda rank, world, batch: BatchStream(ParquetDataset(path, tok, 32, 4096), batch, CollatorForCLM(32, tok.pad_token_id),
+                                                rank=rank, world_size=world, prefetch=0)
+    # written by 2 ranks at batch 2 after 6 batches = 24 samples
+    saved = []
+    for r in range(2):
+        s = mk(r, 2, 2)
+        s.batches_consumed = 6
+        saved.append(s.state_dict())
+    same = mk(1, 2, 2)
+    same.restore(saved)
+    assert same.batches_consumed == 6
+    four = mk(3, 4, 2)              # 24 samples = 3 global batches of 8
+    four.restore(saved)
+    assert four.batches_consumed == 3
+    one = mk(0, 1, 4)               # 24 samples = 6 global batches of 4
+    one.restore(saved)
+    assert one.batches_consumed == 6
+    # the converted stream continues exactly where the old geometry stopped: sample 24 comes next
+    nxt, _ = next(one)
+    ref = mk(0, 1, 1)
+    ref.batches_consumed = 24
+    want, _ = next(ref)
+    assert torch.equal(nxt[0], want[0])
+    bad = mk(0, 1, 5)               # 24 is not a multiple of 5
+    with _pytest.raises(ValueError, match="whole number of global batches"):
+        bad.restore(saved)
+    packed_state = [dict(s, kind="packed") for s in saved]
+    with _pytest.raises(ValueError, match="packed"):
+        mk(0, 1, 4).restore(packed_state)

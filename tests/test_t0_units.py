@@ -150,3 +150,33 @@ def test_c_header_declares_every_entry_point():
         defined |= set(re.findall(r"^FTL_API\s+[\w\s\*]+?\b(ftl_[a-z0-9_]+)\s*\(", open(path).read(), flags=re.M))
     defined.discard("ftl_attn_dbg_read")            # probe build only (FTL_ATTN_DEBUG)
     assert len(defined) > 40 and not (defined - declared), sorted(defined - declared)
+
+
+def test_loader_picks_the_newest_complete_shard_directory(tmp_path):
+    """Crash-safe replacement of a sharded checkpoint: whichever of `.shards`, `.shards.new`, `.shards.old`
+    is complete (has a manifest) and has the largest training_step wins; an incomplete directory is ignored."""
+    import json
+
+    from fault_tolerant_llm_training_b200.ckpt.layout import load_checkpoint
+    from fault_tolerant_llm_training_b200.ckpt.sharded import MANIFEST, best_shard_dir, shard_dir
+
+    base = shard_dir(str(tmp_path), "77")
+
+    def write(d, step, complete=True):
+        os.makedirs(d, exist_ok=True)
+        open(os.path.join(d, "rank0.bin"), "wb").close()
+        if complete:
+            with open(os.path.join(d, MANIFEST), "w") as f:
+                json.dump({"training_step": step, "lr_scheduler": {}, "world_size": 1}, f)
+
+    assert best_shard_dir(str(tmp_path), "77") is None
+    write(base, 10)
+    assert best_shard_dir(str(tmp_path), "77") == base
+    write(base + ".new", 20, complete=False)          # killed while the new shards were being written
+    assert best_shard_dir(str(tmp_path), "77") == base
+    write(base + ".new", 20)                           # manifest durable, killed before the swap
+    assert best_shard_dir(str(tmp_path), "77") == base + ".new"
+    ck = load_checkpoint(str(tmp_path), "77")          # no consolidated file: the loader resumes from the newest shards
+    assert ck["training_step"] == 20 and ck["_sharded_dir"] == base + ".new"
+    os.rename(base, base + ".old")                     # killed inside the swap: only .old and .new exist
+    assert best_shard_dir(str(tmp_path), "77") == base + ".new"
