@@ -1,9 +1,9 @@
 #!/bin/bash
 # compute-sanitizer runs over the small cases of every hand-written kernel.  One tool per gpurun call
 # (B200_PROFILING.md): tools/sanitize.sh memcheck | racecheck | synccheck
-# NOTE (round 1): on the shared B200 pool used for this round `compute-sanitizer` answered "closed on this pool", so
-# this script has not produced a report yet; bad accesses are guarded instead by bounded mbarrier waits (trap after
-# 4 s), small-shape tests with tails (tests/test_native_ops.py) and comparison with fp32 oracles.
+# NOTE (rounds 1 and 2): on the shared B200 pool `compute-sanitizer` answers "closed on this pool and stays closed"
+# (exit 86; profiles/sanitizer_r2.md has the message and the substitutes: bounded waits, tail shapes against fp32
+# oracles, bitwise repeatability, tools/comm_stress.py).
 set -u
 cd "$(dirname "$0")/.."
 TOOL=${1:-memcheck}
