@@ -294,6 +294,8 @@ constexpr int kStaticScratchDim = 4096;
 static __device__ __align__(256) float g_rmsnorm_static_scratch[kStaticScratchRows * kStaticScratchDim];
 
 constexpr int kMaxDevices = 64;
+// Per-device cache of the array's device address, filled on a device's first call WITHOUT a lock: two host threads that
+// make their first call on the same device at the same moment both resolve and store the same value (benign).
 static float* g_static_scratch_ptr[kMaxDevices] = {nullptr};
 static thread_local char g_last_error[256] = "";
 
