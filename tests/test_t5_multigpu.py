@@ -141,12 +141,13 @@ def test_two_rank_usr1_chain_is_bitwise(tmp_path, mode):
 
     mk = lambda steps, *more: TINY + ["--dataset", os.path.join(str(tmp_path), "d.parquet"), "--training-steps", str(steps),
                                       "--parallel", mode] + list(more)
-    full = Job(tmp_path, 9000, mk(60, "--save-final"), nproc=2, timeout=600)
+    # enough steps that the job is still running when the signal arrives (a step of this model takes a few ms)
+    full = Job(tmp_path, 9000, mk(600, "--save-final"), nproc=2, timeout=600)
     assert full.returncode == 0 and "Training completed" in full.text, full.text[-3000:]
-    j1 = Job(tmp_path, 9001, mk(60), nproc=2, signal_at=12, sig=signal.SIGUSR1, timeout=600)
+    j1 = Job(tmp_path, 9001, mk(600), nproc=2, signal_at=12, sig=signal.SIGUSR1, timeout=600)
     assert j1.returncode == 0 and "[EXIT HANDLER] Job timed out, saving checkpoint." in j1.text, j1.text[-3000:]
     assert j1.sbatch_calls == [f"{tmp_path}/train.sh 9001"]
-    j2 = Job(tmp_path, 9002, mk(60, "--save-final", "--checkpoint-id", "9001"), nproc=2, timeout=600)
+    j2 = Job(tmp_path, 9002, mk(600, "--save-final", "--checkpoint-id", "9001"), nproc=2, timeout=600)
     assert j2.returncode == 0 and "Training completed" in j2.text, j2.text[-3000:]
     merged = dict(j1.losses)
     merged.update(j2.losses)
