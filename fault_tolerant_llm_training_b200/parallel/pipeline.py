@@ -111,8 +111,10 @@ class PipelinedTrainer(NativeTrainer):
             self.engine.hook_params = self._wait_params
             self.engine.hook_grads = self._grads_done
             W, T = self.env.world_size, B * S
-            self.sparse_emb = (W > 1 and self.SPARSE_EMB and T <= self.TOK_CAP and len(self.ranges[0]) == 1
-                               and "toks" in self.symm.sizes)
+            can = (W > 1 and self.SPARSE_EMB and T <= self.TOK_CAP and len(self.ranges[0]) == 1
+                   and "toks" in self.symm.sizes)
+            # every rank must take the same path (a rank that owns no part of a very small table would not qualify)
+            self.sparse_emb = bool(W > 1 and self.env.max_int(0 if can else 1) == 0)
             if self.sparse_emb:
                 self.engine.hook_tokens = self._push_tokens
                 self.engine.sparse_emb_zero = True       # the backward clears only its own previous rows: no 1 GB memset
