@@ -47,7 +47,7 @@ constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kAByte
 constexpr int kGemmThreads = 192;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 
-enum { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_ROPE = 2, EPI_SWIGLU_BWD = 3 };
+enum { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_ROPE = 2, EPI_SWIGLU_BWD = 3, EPI_ACC32 = 4 };
 
 struct GemmArgs {
     __nv_bfloat16* C;       // PLAIN/ROPE: [M, N]; SWIGLU: act [M, N/2]
@@ -59,6 +59,8 @@ struct GemmArgs {
     const __nv_bfloat16* in_gate;   // SWIGLU_BWD: saved pre-activations [M, N] (ldc)
     const __nv_bfloat16* in_up;
     float* sumsq;           // optional [gridDim.x * 4]: sum of squares of the bf16 outputs per (CTA, epilogue warp)
+    float* C32;             // optional fp32 [M, N] (ldc) accumulator across calls (chunked reductions): see acc_mode
+    int acc_mode;           // EPI_ACC32: bit 0 = add to the old C32 (else overwrite it), bit 1 = also write C = bf16(C32)
     int64_t ldc;
     int M, N, K;            // N counts accumulator columns (SWIGLU: 2 x hidden)
     int nk1;                // k-blocks served by the first (A, B) pair; the rest come from the second
@@ -280,6 +282,21 @@ __device__ __forceinline__ void epilogue_tile(const GemmArgs& g, uint32_t taddr,
                                         f[2 * j + 1] = a * ss[j] + b * cc[j];
                                     }
                                 }
+                                if (kEpi == EPI_ACC32 && col < g.N) {
+                                    // fp32 running sum over several launches (e.g. the vocabulary chunks of the LM head):
+                                    // one 32-byte read-modify-write per 8 columns; bf16 is written by the last launch only
+                                    float* p32 = g.C32 + (int64_t)row * g.ldc + col;
+                                    if (g.acc_mode & 1) {
+                                        uint32_t old[8];
+                                        ld_row32(p32, old);
+    #pragma unroll
+                                        for (int j = 0; j < 8; ++j) f[j] += __uint_as_float(old[j]);
+                                    }
+                                    uint32_t nw[8];
+    #pragma unroll
+                                    for (int j = 0; j < 8; ++j) nw[j] = __float_as_uint(f[j]);
+                                    st8f(p32, nw);
+                                }
                                 o[v] = pack8(f);
                                 if (kEpi == EPI_PLAIN && g.sumsq != nullptr && col < g.N) {   // norm² of what is stored
                                     float q[8];
@@ -288,7 +305,8 @@ __device__ __forceinline__ void epilogue_tile(const GemmArgs& g, uint32_t taddr,
                                     for (int j = 0; j < 8; ++j) ss += q[j] * q[j];
                                 }
                             }
-                            store_groups(g.C, w_c, (int64_t)row * g.ldc + n0 + c, o, n0 + c, g.N);
+                            if (kEpi != EPI_ACC32 || (g.acc_mode & 2))
+                                store_groups(g.C, w_c, (int64_t)row * g.ldc + n0 + c, o, n0 + c, g.N);
                         }
                     }
                 }
@@ -810,6 +828,28 @@ FTL_API int ftl_gemm_bf16_ex(const void* a, int64_t lda, int a_mn, const void* b
     if (!a_mn && b_mn) return launch<EPI_PLAIN, false, true>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
     if (a_mn && b_mn) return launch<EPI_PLAIN, true, true>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
     return launch<EPI_PLAIN, true, false>(csel, ta, tb, ta2, tb2, g, max_ctas, stream);
+}
+
+// C32 (+)= A.B in fp32 across several calls.  mode bit 0: add to what c32 holds (else overwrite it); bit 1: also write
+// the bf16 result to c (c may be NULL otherwise).  c32: fp32 [M, N], same leading dimension ldc (elements), 32-byte aligned.
+// a: [M, K] row-major; b: [K, N] row-major (the dgrad form dY @ W).
+FTL_API int ftl_gemm_bf16_acc32(const void* a, int64_t lda, const void* b, int64_t ldb, void* c, float* c32, int64_t ldc,
+                                int M, int N, int K, int mode, int max_ctas, cudaStream_t stream) {
+    if (M <= 0 || N <= 0 || K <= 0 || (N % 8) || (ldc % 8) || (lda % 8) || (ldb % 8) || mode < 0 || mode > 3 || !c32 ||
+        (reinterpret_cast<uintptr_t>(c32) & 31) || ((mode & 2) && !c))
+        return (int)cudaErrorInvalidValue;
+    CUtensorMap ta, tb;
+    int e;
+    if ((e = make_tmap(&ta, a, M, K, lda, BK, BM))) return e;
+    const int csel = gemm_cluster(b, nullptr);
+    if ((e = make_tmap(&tb, b, K, N, ldb, 64, BK))) return e;
+    GemmArgs g{};
+    g.C = (__nv_bfloat16*)c;
+    g.C32 = c32; g.acc_mode = mode;
+    g.ldc = ldc;
+    g.M = M; g.N = N; g.K = K;
+    g.nk1 = (K + BK - 1) / BK;
+    return launch<EPI_ACC32, false, true>(csel, ta, tb, ta, tb, g, max_ctas, stream);
 }
 
 FTL_API int ftl_gemm_bf16(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c,

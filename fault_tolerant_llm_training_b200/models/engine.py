@@ -218,7 +218,12 @@ class NativeEngine:
         self.ff = bf(T, d)
         self.xf = bf(T, d)                               # final normed stream
         self.rstd_f = f32(T)
-        self.logits = bf(T, V)
+        # FTL_FUSED_HEAD=1: vocabulary-chunked LM head + cross-entropy, no [T, V] buffer (ops/fused_head.py)
+        self.head = None
+        if self.USE_TC and os.environ.get("FTL_FUSED_HEAD", "0") == "1":
+            from ..ops.fused_head import ChunkedHead
+            self.head = ChunkedHead(T, d, V, device, chunk=int(os.environ.get("FTL_HEAD_CHUNK", "8192")))
+        self.logits = bf(T, V) if self.head is None else None
         self.row_loss = f32(T)
         self.loss = f32(1)
         # backward transients
@@ -273,7 +278,8 @@ class NativeEngine:
             return False
         c = self.cfg
         gs, ns = N.gemm_sumsq_slots(), N.rmsnorm_sumsq_slots(c.dim)
-        n = c.n_layers * (5 * gs + 2 * ns) + gs + ns + self.T
+        head_gemms = self.head.n_chunks if self.head is not None else 1     # one weight-gradient GEMM per vocabulary chunk
+        n = c.n_layers * (5 * gs + 2 * ns) + head_gemms * gs + ns + self.T
         self.norm_arena = torch.zeros(n, dtype=torch.float32, device=self.dev)
         return True
 
@@ -403,8 +409,12 @@ class NativeEngine:
         self._need(L + 1)
         # x_L = h_{L-1} + ff, fused with the final norm
         N.rmsnorm_fwd(self.h[L - 1], self.w_fn, c.norm_eps, self.xf, self.rstd_f, delta=self.ff, h_out=self.x[L])
-        self.gemm_nt(self.xf, self.w_out, self.logits)
-        N.cross_entropy(self.logits, labels.view(-1), inv_n, self.row_loss, self.loss, write_grad=write_grad)
+        if self.head is not None:
+            self.head.forward(self.xf, self.w_out, labels.view(-1), inv_n, self.row_loss, self.loss)
+            self._head_args = (labels.view(-1), inv_n)      # the backward recomputes the logits chunk by chunk
+        else:
+            self.gemm_nt(self.xf, self.w_out, self.logits)
+            N.cross_entropy(self.logits, labels.view(-1), inv_n, self.row_loss, self.loss, write_grad=write_grad)
         _Nvtx.pop()
         _Nvtx.pop()
         return self.loss
@@ -424,8 +434,12 @@ class NativeEngine:
         _Nvtx.push("bwd head")
         if self.hook_params_bwd is not None:
             self.hook_params_bwd(L + 1)
-        self.gemm_tn(dl, self.xf, self.g_out)                     # dW_out
-        self.gemm_nn(dl, self.w_out, self.dtmp)                   # d xf
+        if self.head is not None:
+            labels, inv_n = self._head_args
+            self.head.backward(self.xf, self.w_out, labels, inv_n, self.g_out, self.dtmp, sumsq=self._sq_gemm)
+        else:
+            self.gemm_tn(dl, self.xf, self.g_out)                     # dW_out
+            self.gemm_nn(dl, self.w_out, self.dtmp)                   # d xf
         dx, spare = self.dx_a, self.dx_b
         N.rmsnorm_bwd(self.dtmp, self.x[L], self.w_fn, self.rstd_f, dx, self.g_fn, self.norm_scratch, sumsq=self._sq_norm())
         if self.hook_grads is not None:

@@ -106,6 +106,10 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_nvls_adamw_allgather", [P, P, P, P, P, I64, I64, P, P, P, P, I, P])
     _sig(L, "ftl_emb_tokens_push", [P, P, I64, I, I, I, I, P])
     _sig(L, "ftl_emb_sparse_reduce", [P, I, I, P, P, I, I, I64, I, I, I64, I64, P, P, P])
+    _sig(L, "ftl_ce_chunk_stats", [P, I64, P, I, I, I, I, P, P, P, I64, P])
+    _sig(L, "ftl_ce_combine", [P, P, P, P, I, I64, I, P, P, P, P, P])
+    _sig(L, "ftl_ce_chunk_grad", [P, I64, P, I, I, I, P, P, I64, P])
+    _sig(L, "ftl_gemm_bf16_acc32", [P, I64, P, I64, P, P, I64, I, I, I, I, I, P])
     for name, sig in _OPTIONAL.items():
         if hasattr(L, name):
             _sig(L, name, sig[0], sig[1] if len(sig) > 1 else c_int)
@@ -226,6 +230,38 @@ def cross_entropy(logits, labels, inv_n, row_loss, loss_out, row_lse=None, write
     _check(lib().ftl_cross_entropy(_ptr(logits), _ptr(labels), _ptr(inv_n), _ptr(row_loss), _ptr(row_lse),
                                    _ptr(loss_out), rows, vocab, logits.stride(0), int(write_grad), _stream()),
            "ftl_cross_entropy", 2 if loss_out is not None else 1)
+
+
+def ce_chunk_stats(chunk, labels, col0, n_chunks, c, cmax, csum, picked):
+    """Pass 1 of the chunked head for chunk c = logits of columns [col0, col0 + chunk.shape[1])."""
+    rows, width = chunk.shape
+    _check(lib().ftl_ce_chunk_stats(_ptr(chunk), chunk.stride(0), _ptr(labels), col0, width, n_chunks, c, _ptr(cmax),
+                                    _ptr(csum), _ptr(picked), rows, _stream()), "ftl_ce_chunk_stats")
+
+
+def ce_combine(cmax, csum, picked, labels, n_chunks, vocab, inv_n, lse, row_loss, loss_out):
+    _check(lib().ftl_ce_combine(_ptr(cmax), _ptr(csum), _ptr(picked), _ptr(labels), n_chunks, labels.numel(), vocab,
+                                _ptr(inv_n), _ptr(lse), _ptr(row_loss), _ptr(loss_out), _stream()), "ftl_ce_combine",
+           2 if loss_out is not None else 1)
+
+
+def ce_chunk_grad(chunk, labels, col0, vocab, lse, inv_n):
+    """Pass 2: the recomputed chunk of logits becomes (softmax - onehot) * inv_n in place."""
+    rows, width = chunk.shape
+    _check(lib().ftl_ce_chunk_grad(_ptr(chunk), chunk.stride(0), _ptr(labels), col0, width, vocab, _ptr(lse), _ptr(inv_n),
+                                   rows, _stream()), "ftl_ce_chunk_grad")
+
+
+def gemm_acc32(a, b, c32, mode, out=None, max_ctas=0):
+    """c32 (+)= a [M, K] @ b [K, N] in fp32 across calls; mode bit 0 = add to c32 (else overwrite), bit 1 = also write
+    the bf16 result to `out`."""
+    _mat(a), _mat(b)
+    M, K = a.shape
+    Nn = b.shape[1]
+    assert b.shape[0] == K and c32.dtype == torch.float32 and c32.shape == (M, Nn) and c32.is_contiguous()
+    assert out is None or (_mat(out) is out and out.shape == (M, Nn) and out.stride(0) == Nn)
+    _check(lib().ftl_gemm_bf16_acc32(_ptr(a), a.stride(0), _ptr(b), b.stride(0), _ptr(out), _ptr(c32), Nn, M, Nn, K, mode,
+                                     max_ctas, _stream()), "ftl_gemm_bf16_acc32")
 
 
 def grad_norm_partials() -> int:

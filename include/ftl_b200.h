@@ -72,6 +72,19 @@ int ftl_embedding_bwd_direct(const int64_t* tokens, const int64_t* prev_tokens, 
 int ftl_cross_entropy(void* logits, const int64_t* labels, const float* inv_n, float* row_loss, float* row_lse,
                       float* loss_out, int64_t rows, int vocab, int64_t ld, int write_grad, ftl_stream_t stream);
 
+/* Vocabulary-chunked LM head + cross-entropy (the [T, V] logits are never held; reference: model.py:379 +
+ * train.py:100-103).  Per chunk c of columns [col0, col0 + width): run the head GEMM into a [rows, width] buffer, then
+ * ftl_ce_chunk_stats; after the last chunk ftl_ce_combine gives lse / row losses / loss.  Backward: recompute the chunk,
+ * ftl_ce_chunk_grad turns it into d(logits) in place, and the two gradient GEMMs read it (ftl_gemm_bf16_acc32 keeps the
+ * running d(hidden) in fp32 across chunks). */
+int ftl_ce_chunk_stats(const void* chunk, int64_t ld, const int64_t* labels, int col0, int width, int n_chunks, int c,
+                       float* cmax, float* csum, float* picked, int64_t rows, ftl_stream_t stream);
+int ftl_ce_combine(const float* cmax, const float* csum, const float* picked, const int64_t* labels, int n_chunks,
+                   int64_t rows, int vocab, const float* inv_n, float* lse, float* row_loss, float* loss_out,
+                   ftl_stream_t stream);
+int ftl_ce_chunk_grad(void* chunk, int64_t ld, const int64_t* labels, int col0, int width, int vocab, const float* lse,
+                      const float* inv_n, int64_t rows, ftl_stream_t stream);
+
 /* ---- Gradient norm + fused AdamW over flat bf16 buffers — reference: utils.py:58-63, train.py:68,107-109 ----
  * hyper (fp32[8]) = lr, beta1, beta2, eps, weight_decay, 1-beta1^t, sqrt(1-beta2^t), max_norm
  * stats (fp32[4]) = grad_norm, clip_coef, finite, sum of squares */
@@ -94,6 +107,11 @@ int ftl_gemm_sumsq_slots(void);
 int ftl_gemm_bf16_ex(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* c, int64_t ldc,
                      int M, int N, int K, const void* a2, int64_t lda2, const void* b2, int64_t ldb2, int K2,
                      float* sumsq, int max_ctas, ftl_stream_t stream);
+/* c32 (+)= a [M,K] @ b [K,N] with an fp32 running sum across calls.  mode bit 0: add to what c32 holds (else overwrite);
+ * bit 1: also write the bf16 result to c (c may be NULL otherwise).  c32: fp32 [M, N], leading dimension ldc, 32-byte
+ * aligned.  No counterpart in the reference (autograd accumulates the head's input gradient in one GEMM). */
+int ftl_gemm_bf16_acc32(const void* a, int64_t lda, const void* b, int64_t ldb, void* c, float* c32, int64_t ldc, int M,
+                        int N, int K, int mode, int max_ctas, ftl_stream_t stream);
 /* SwiGLU backward in the epilogue of the w2 dgrad GEMM: dact = dx [M,K] @ w2 [K,H] stays in TMEM; reads the saved
  * gate / up, writes dgate / dup (all [M,H], leading dimension ldo; H, ldo multiples of 16) — autograd of model.py:254 */
 int ftl_gemm_swiglu_bwd(const void* dx, int64_t lddx, const void* w2, int64_t ldw, const void* gate, const void* up,

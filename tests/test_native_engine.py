@@ -29,12 +29,18 @@ def _batch(seed=0, B=2):
     return inputs, labels
 
 
-def test_engine_loss_and_grads_match_autograd():
+@pytest.mark.parametrize("fused_head", [False, True])
+def test_engine_loss_and_grads_match_autograd(fused_head, monkeypatch):
+    if fused_head:   # vocabulary-chunked LM head + cross-entropy: 4 chunks of 256 columns, no [T, V] buffer
+        monkeypatch.setenv("FTL_FUSED_HEAD", "1")
+        monkeypatch.setenv("FTL_HEAD_CHUNK", "256")
     tr = _trainer()
     ref = build_model(CFG, torch.float32, "cuda", seed=0)
     ref.load_state_dict({k: v.float() for k, v in tr.model.state_dict().items()})
     inputs, labels = _batch()
     tr._ensure_engine(*inputs.shape)
+    assert (tr.engine.head is not None and tr.engine.logits is None and tr.engine.head.n_chunks == 4) if fused_head \
+        else tr.engine.head is None
     n = int(labels.ne(-100).sum())
     inv_n = torch.tensor([1.0 / n], device="cuda")
     loss = tr.engine.forward(inputs.cuda(), labels.cuda(), inv_n)

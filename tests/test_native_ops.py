@@ -353,3 +353,38 @@ def test_embedding_bwd_direct(N, V, D, n):
     want = torch.zeros_like(dt)
     N.embedding_bwd_direct(tok2, None, dout2, want)
     assert torch.equal(dt, want)
+
+
+@pytest.mark.parametrize("rows,V,dim,chunk", [(256, 131072, 512, 8192), (192, 4096, 256, 1024)])
+def test_chunked_head_matches_fp32_cross_entropy(N, rows, V, dim, chunk):
+    """LM head + cross-entropy without the [T, V] logits (ops/fused_head.py) against fp32 F.cross_entropy on the full
+    logits: loss rtol 1e-4-ish (bf16 logits), dX / dW relative error < 1e-2, gradient-norm partials, repeatable."""
+    from fault_tolerant_llm_training_b200.ops.fused_head import ChunkedHead
+    x, w = bf(rows, dim, scale=1.0, seed=1), bf(V, dim, scale=0.05, seed=2)
+    g = torch.Generator(device=DEV).manual_seed(4)
+    labels = torch.randint(0, V, (rows,), device=DEV, generator=g)
+    labels[::9] = -100
+    n = int(labels.ne(-100).sum())
+    inv_n = torch.tensor([1.0 / n], device=DEV)
+    head = ChunkedHead(rows, dim, V, torch.device(DEV), chunk=chunk)
+    assert head.n_chunks == V // chunk and head.buf.numel() == rows * chunk
+    row_loss, loss = torch.empty(rows, device=DEV), torch.empty(1, device=DEV)
+    head.forward(x, w, labels, inv_n, row_loss, loss)
+    dw, dx = torch.empty_like(w), torch.empty_like(x)
+    slots = [torch.zeros(N.gemm_sumsq_slots(), device=DEV) for _ in range(head.n_chunks)]
+    it = iter(slots)
+    head.backward(x, w, labels, inv_n, dw, dx, sumsq=lambda: next(it))
+    # fp32 oracle on the same bf16 inputs; logits rounded to bf16 like the Linear's output (model.py:379)
+    xf, wf = x.float().requires_grad_(), w.float().requires_grad_()
+    logits = (xf @ wf.t())
+    ref = torch.nn.functional.cross_entropy(logits, labels, ignore_index=-100, reduction="sum") / n
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 2e-3 * abs(float(ref))
+    assert _rel(dx, xf.grad) < 1e-2 and _rel(dw, wf.grad) < 1e-2
+    total = sum(float(s.sum()) for s in slots)
+    assert abs(total - float(dw.float().pow(2).sum())) < 1e-3 * total
+    # the same thing again gives the same bits
+    loss2, dw2, dx2 = torch.empty(1, device=DEV), torch.empty_like(w), torch.empty_like(x)
+    head.forward(x, w, labels, inv_n, row_loss, loss2)
+    head.backward(x, w, labels, inv_n, dw2, dx2)
+    assert torch.equal(loss, loss2) and torch.equal(dw, dw2) and torch.equal(dx, dx2)
