@@ -70,14 +70,17 @@ __global__ void raise_abort_kernel(uint32_t* const* __restrict__ peer_flags, int
 template <int W>
 __global__ void __launch_bounds__(512)
 dp_reduce_scatter_kernel(__nv_bfloat16* const* __restrict__ peer_g, int rank, int64_t lo_vec, int64_t nvec,
-                         float* __restrict__ partial, const uint32_t* __restrict__ status) {
+                         float* __restrict__ partial, const uint32_t* __restrict__ status,
+                         __nv_bfloat16* __restrict__ dst_compact) {
     __shared__ float red[33];
     float acc = 0.f;
     if (*status == 0) {
         const __nv_bfloat16* src[W];
 #pragma unroll
         for (int r = 0; r < W; ++r) src[r] = peer_g[r] + lo_vec * 8;
-        __nv_bfloat16* dst = peer_g[rank] + lo_vec * 8;
+        // in place (this rank's own range of its gradient buffer) or into a compact shard buffer (fully-sharded mode
+        // with gradient slots that the backward reuses)
+        __nv_bfloat16* dst = dst_compact ? dst_compact : peer_g[rank] + lo_vec * 8;
         for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
             int4 raw[W];
 #pragma unroll
@@ -91,7 +94,7 @@ dp_reduce_scatter_kernel(__nv_bfloat16* const* __restrict__ peer_g, int rank, in
                 for (int j = 0; j < 8; ++j) s[j] += f[j];
             }
             const bf16x8 o = pack8(s);
-            if (W > 1) st8(dst + i * 8, o);   // a single rank already holds the sum
+            if (W > 1 || dst_compact) st8(dst + i * 8, o);   // a single rank already holds the sum in place
             float f[8];
             unpack8(o, f);
 #pragma unroll
@@ -387,7 +390,23 @@ FTL_API int ftl_dp_reduce_scatter(void* const* peer_g, int rank, int world, int6
     const int grid = ftl_dp_partials(max_ctas);
     auto P = (__nv_bfloat16* const*)peer_g;
     auto S = (const uint32_t*)status;
-#define RS_CASE(W) case W: dp_reduce_scatter_kernel<W><<<grid, 512, 0, stream>>>(P, rank, lo / 8, n / 8, partial, S); break;
+#define RS_CASE(W) case W: dp_reduce_scatter_kernel<W><<<grid, 512, 0, stream>>>(P, rank, lo / 8, n / 8, partial, S, nullptr); break;
+    switch (world) { RS_CASE(1) RS_CASE(2) RS_CASE(3) RS_CASE(4) RS_CASE(5) RS_CASE(6) RS_CASE(7) RS_CASE(8)
+        default: return (int)cudaErrorInvalidValue; }
+#undef RS_CASE
+    FTL_LAUNCH_CHECK();
+    return 0;
+}
+
+// Same reduction, but the bf16 sum of [lo, lo+n) goes to dst[0, n) (a compact shard buffer) instead of in place.
+FTL_API int ftl_dp_reduce_scatter_to(void* const* peer_g, int rank, int world, int64_t lo, int64_t n, void* dst,
+                                     float* partial, const void* status, int max_ctas, cudaStream_t stream) {
+    if (lo % 8 || n % 8 || n <= 0 || !dst || (reinterpret_cast<uintptr_t>(dst) & 15)) return (int)cudaErrorInvalidValue;
+    const int grid = ftl_dp_partials(max_ctas);
+    auto P = (__nv_bfloat16* const*)peer_g;
+    auto S = (const uint32_t*)status;
+#define RS_CASE(W) case W: dp_reduce_scatter_kernel<W><<<grid, 512, 0, stream>>>(P, rank, lo / 8, n / 8, partial, S, \
+        (__nv_bfloat16*)dst); break;
     switch (world) { RS_CASE(1) RS_CASE(2) RS_CASE(3) RS_CASE(4) RS_CASE(5) RS_CASE(6) RS_CASE(7) RS_CASE(8)
         default: return (int)cudaErrorInvalidValue; }
 #undef RS_CASE

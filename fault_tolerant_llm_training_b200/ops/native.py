@@ -71,6 +71,7 @@ def lib() -> ctypes.CDLL:
     _sig(L, "ftl_raise_abort", [P, I, P])
     _sig(L, "ftl_dp_partials", [I])
     _sig(L, "ftl_dp_reduce_scatter", [P, I, I, I64, I64, P, P, I, P])
+    _sig(L, "ftl_dp_reduce_scatter_to", [P, I, I, I64, I64, P, P, P, I, P])
     _sig(L, "ftl_dp_publish", [P, I, P, P, I, I, P])
     _sig(L, "ftl_dp_finalize", [P, I, P, P, P, I, P, P, P])
     _sig(L, "ftl_dp_adamw_allgather", [P, P, P, P, I, I, I64, I64, P, P, P, P, I, P])
@@ -405,6 +406,14 @@ def emb_sparse_reduce(peer_g, rank, world, toks, toks_prev, T, cap, emb_off, dim
     assert partial.dtype == torch.float32 and partial.numel() >= world * T
     _check(lib().ftl_emb_sparse_reduce(_ptr(peer_g), rank, world, _ptr(toks), _ptr(toks_prev), T, cap, emb_off, dim, vocab,
                                        lo, hi, _ptr(partial), _ptr(status), _stream()), "ftl_emb_sparse_reduce")
+
+
+def dp_reduce_scatter_to(peer_g, rank, world, lo, n, dst, partial, status, max_ctas=0):
+    """Like dp_reduce_scatter, but the reduced range lands in the compact buffer `dst` (n elements)."""
+    _bf16(dst)
+    assert dst.numel() >= n
+    _check(lib().ftl_dp_reduce_scatter_to(_ptr(peer_g), rank, world, lo, n, _ptr(dst), _ptr(partial), _ptr(status), max_ctas,
+                                          _stream()), "ftl_dp_reduce_scatter_to")
 
 
 def dp_publish(partial, nparts, loss_local, peer_slots, rank, world):

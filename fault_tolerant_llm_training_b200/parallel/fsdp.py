@@ -49,11 +49,27 @@ class _Unit:
 
 
 class FsdpState(FlatState):
-    """Flat gradient buffer as usual; parameters are views into the staging memory: `slot_of(bucket)` returns the
-    staging tensor that holds the bucket and the flat offset of its first element."""
+    """Parameters are views into the staging memory: `slot_of(bucket)` returns the staging tensor that holds the bucket
+    and the flat offset of its first element.  Gradients are views into the flat gradient buffer, or — with sharded
+    gradients — into the buffer `gslot_of(bucket)` names the same way."""
 
-    def bind_slots(self, slot_of, bucket_of: Dict[str, int]) -> None:
-        self._slot_of, self._bucket_of = slot_of, bucket_of
+    def bind_slots(self, slot_of, bucket_of: Dict[str, int], gslot_of=None) -> None:
+        self._slot_of, self._bucket_of, self._gslot_of = slot_of, bucket_of, gslot_of
+
+    def grad_view(self, name: str) -> torch.Tensor:
+        if self._gslot_of is None:
+            return super().grad_view(name)
+        off, n, shape = self.index[name]
+        buf, base = self._gslot_of(self._bucket_of[name])
+        return buf[off - base:off - base + n].view(shape)
+
+    def grad_span(self, first: str, last: str, shape) -> torch.Tensor:
+        if self._gslot_of is None:
+            return super().grad_span(first, last, shape)
+        o0, _, _ = self.index[first]
+        o1, n1, _ = self.index[last]
+        buf, base = self._gslot_of(self._bucket_of[first])
+        return buf[o0 - base:o1 + n1 - base].view(shape)
 
     def param_view(self, name: str) -> torch.Tensor:
         off, n, shape = self.index[name]
@@ -123,7 +139,20 @@ class FsdpTrainer(PipelinedTrainer):
         flag_words = N.lib().ftl_comm_flag_words()
         # fully-sharded mode has no parameter broadcast; its gradient reduce-scatter can go through the switch too
         self.nvls = os.environ.get("FTL_COLLECTIVE", "p2p") == "nvls" and W > 1
-        self.symm = make_symmetric(env, dict({"own": self.own_numel * 2, "g": numel * 2, "flags": flag_words * 4, "slots": 64},
+        # FTL_FSDP_SHARD_GRADS=1: no model-sized gradient buffer.  The embedding and the head bucket keep their own
+        # gradient buffers, the layers write into two layer-sized slots by bucket parity, and every reduce-scatter leaves
+        # its result in a compact shard buffer; a slot is reused by the backward two layers later, once every rank has
+        # finished reading it (a barrier after the reduce-scatter + an event the compute stream waits on).
+        self.shard_grads = os.environ.get("FTL_FSDP_SHARD_GRADS", "0") == "1" and W > 1
+        if self.shard_grads and self.nvls:
+            raise ValueError("FTL_FSDP_SHARD_GRADS=1 uses the peer-load reduce-scatter; unset FTL_COLLECTIVE=nvls")
+        if self.shard_grads:
+            layer_max = max(hi - lo for lo, hi in self.buckets[1:L + 1])
+            gsizes = {"g0": (self.buckets[0][1] - self.buckets[0][0]) * 2,
+                      "gL": (self.buckets[L + 1][1] - self.buckets[L + 1][0]) * 2, "gs0": layer_max * 2, "gs1": layer_max * 2}
+        else:
+            gsizes = {"g": numel * 2}
+        self.symm = make_symmetric(env, dict({"own": self.own_numel * 2, "flags": flag_words * 4, "slots": 64}, **gsizes,
                                              **self._tok_buffers()), multicast=("g",) if self.nvls else ())
         self.p_own = self.symm.tensor("own", torch.bfloat16)
         self.m_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
@@ -145,8 +174,13 @@ class FsdpTrainer(PipelinedTrainer):
                     src = params[u.name].reshape(-1)
                 self.p_own[u.coff:u.coff + u.shard].copy_(src[env.rank * u.shard:(env.rank + 1) * u.shard])
             del full
+        if self.shard_grads:
+            self.gbufs = {k: self.symm.tensor(k, torch.bfloat16) for k in ("g0", "gL", "gs0", "gs1")}
+            self.g_own = torch.zeros(self.own_numel, dtype=torch.bfloat16, device=self.device)
+            self.ev_gfree = [torch.cuda.Event(), torch.cuda.Event()]
         bufs = {"p": lambda n: torch.zeros(0, dtype=torch.bfloat16, device=self.device),   # no full parameter buffer
-                "g": lambda n: self.symm.tensor("g", torch.bfloat16),
+                "g": lambda n: (torch.zeros(0, dtype=torch.bfloat16, device=self.device) if self.shard_grads
+                                else self.symm.tensor("g", torch.bfloat16)),
                 "m": lambda n: torch.zeros(0, dtype=torch.bfloat16, device=self.device),
                 "v": lambda n: torch.zeros(0, dtype=torch.bfloat16, device=self.device)}
         flat = FsdpState.__new__(FsdpState)
@@ -156,7 +190,7 @@ class FsdpTrainer(PipelinedTrainer):
         bucket_of = {}
         for name, (off, n, shape) in index.items():
             bucket_of[name] = max(b for b, (lo, hi) in enumerate(self.buckets) if lo <= off)
-        flat.bind_slots(self._slot_of, bucket_of)
+        flat.bind_slots(self._slot_of, bucket_of, self._gslot_of if self.shard_grads else None)
         with torch.no_grad():
             for name, prm in self.model.named_parameters():
                 off, n, shape = index[name]
@@ -205,6 +239,46 @@ class FsdpTrainer(PipelinedTrainer):
         """(staging tensor, flat offset of its first element) for bucket b."""
         return (self.stage[b % 2], self.buckets[b][0]) if self.reshard else (self.stage[0], 0)
 
+    def _gname(self, b: int) -> str:
+        """Name of the gradient buffer that bucket b's gradients are written to (sharded gradients)."""
+        L = self.cfg.n_layers
+        return "g0" if b == 0 else ("gL" if b == L + 1 else f"gs{b % 2}")
+
+    def _gslot_of(self, b: int):
+        return self.gbufs[self._gname(b)], self.buckets[b][0]
+
+    def _emb_grad_location(self):
+        if not self.shard_grads:
+            return super()._emb_grad_location()
+        u, r = self.bucket_units[0][0], self.env.rank
+        base = self.buckets[0][0]
+        return self.symm.table("g0"), u.off - base, u.off - base + r * u.shard, u.off - base + (r + 1) * u.shard
+
+    def _grads_done(self, b: int) -> None:
+        if not self.shard_grads:
+            return super()._grads_done(b)
+        env, L = self.env, self.cfg.n_layers
+        self.ev_grad[b].record()
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(self.ev_grad[b])
+            self._barrier()          # every rank's bucket-b gradients are complete
+            if b == 0 and getattr(self, "sparse_emb", False):
+                self._reduce_embedding_sparse()      # in place in the embedding's own gradient buffer
+                return
+            table, base = self.symm.table(self._gname(b)), self.buckets[b][0]
+            for u, k in zip(self.bucket_units[b], self.range_slot[b]):
+                part = self.rs_partials[k * self.parts:(k + 1) * self.parts]
+                lo = u.off - base + env.rank * u.shard
+                ctas = self.RS_LAST_CTAS if b == 0 else self.RS_CTAS
+                if b == 0:           # dense fallback for the embedding: in place, as in the unsharded layout
+                    N.dp_reduce_scatter(table, env.rank, env.world_size, lo, u.shard, part, self.comm_status, max_ctas=ctas)
+                else:
+                    N.dp_reduce_scatter_to(table, env.rank, env.world_size, lo, u.shard, self.g_own[u.coff:u.coff + u.shard],
+                                           part, self.comm_status, max_ctas=ctas)
+            if 1 <= b <= L:
+                self._barrier()      # every rank has finished reading this slot: the backward may write it again
+                self.ev_gfree[b % 2].record()
+
     def _owned_ranges(self, flat) -> List[List[Tuple[int, int]]]:
         r = self.env.rank
         return [[(u.off + r * u.shard, u.off + (r + 1) * u.shard) for u in us] for us in self.bucket_units]
@@ -252,6 +326,8 @@ class FsdpTrainer(PipelinedTrainer):
     def _params_for_backward(self, b: int) -> None:
         """Backward: the engine is about to read bucket b (all kernels of buckets > b are already enqueued)."""
         main = torch.cuda.current_stream()
+        if self.shard_grads and 1 <= b <= self.cfg.n_layers - 2:
+            main.wait_event(self.ev_gfree[b % 2])     # bucket b + 2's gradients have been reduced out of this slot everywhere
         self._gather(b, include_fused=True)
         main.wait_event(self.ev_gather[b])
         if b - 1 >= 1:
@@ -284,7 +360,13 @@ class FsdpTrainer(PipelinedTrainer):
         r = self.env.rank
         for u in self.bucket_units[b]:
             lo = u.off + r * u.shard
-            N.adamw_shard(self.p_own[u.coff:u.coff + u.shard], self.flat.g[lo:lo + u.shard],
+            if not self.shard_grads:
+                g = self.flat.g[lo:lo + u.shard]
+            elif b == 0:             # reduced in place in the embedding's own buffer
+                g = self.gbufs["g0"][lo - self.buckets[0][0]:lo - self.buckets[0][0] + u.shard]
+            else:
+                g = self.g_own[u.coff:u.coff + u.shard]
+            N.adamw_shard(self.p_own[u.coff:u.coff + u.shard], g,
                           self.m_own[u.coff:u.coff + u.shard], self.v_own[u.coff:u.coff + u.shard], hyper, self.stats,
                           self.comm_status, self.commits, max_ctas=self.UPD_CTAS)
 

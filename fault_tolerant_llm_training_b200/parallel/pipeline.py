@@ -172,13 +172,18 @@ class PipelinedTrainer(NativeTrainer):
         W, cap, e = self.env.world_size, self.TOK_CAP, self.engine
         cur = self.toks_local[self._tok_slot * W * cap:]
         prev = self.toks_local[((self._tok_step - 1) % 3) * W * cap:] if self._have_prev else None
-        (a, hi), = self.ranges[0]
-        emb_off = self.flat.index["tok_embeddings.weight"][0]
+        table, emb_off, a, hi = self._emb_grad_location()
         tail = self.rs_partials[self.rs_partials.numel() - W * e.T:]
-        N.emb_sparse_reduce(self.symm.table("g"), self.env.rank, W, cur, prev, e.T, cap, emb_off, self.cfg.dim,
+        N.emb_sparse_reduce(table, self.env.rank, W, cur, prev, e.T, cap, emb_off, self.cfg.dim,
                             self.cfg.vocab_size, a, hi, tail, self.comm_status)
         self._tok_step += 1
         self._have_prev = True
+
+    def _emb_grad_location(self):
+        """(peer table of the buffer holding the embedding gradient, element offset of the table in it, this rank's
+        element range [lo, hi) in it)."""
+        (a, hi), = self.ranges[0]
+        return self.symm.table("g"), self.flat.index["tok_embeddings.weight"][0], a, hi
 
     # ---- step pieces ---------------------------------------------------------------------------------------------
     def _begin_step(self, hyper: torch.Tensor) -> None:

@@ -199,6 +199,8 @@ int ftl_emb_sparse_reduce(void* const* peer_g, int rank, int world, const int64_
 int ftl_dp_partials(int max_ctas);                              /* floats of `partial` one reduce-scatter launch writes */
 /* gradient range [lo, lo+n) of every rank summed in rank order into this rank's buffer, with the sum of squares of the
  * result in `partial` (reduce-scatter fused with the norm) */
+int ftl_dp_reduce_scatter_to(void* const* peer_g, int rank, int world, int64_t lo, int64_t n, void* dst, float* partial,
+                             const void* status, int max_ctas, ftl_stream_t stream);   /* sum goes to dst[0, n) */
 int ftl_dp_reduce_scatter(void* const* peer_g, int rank, int world, int64_t lo, int64_t n, float* partial,
                           const void* status, int max_ctas, ftl_stream_t stream);
 int ftl_dp_publish(const float* partial, int nparts, const float* loss_local, void* const* peer_slots, int rank,

@@ -155,3 +155,13 @@ def test_two_rank_usr1_chain_is_bitwise(tmp_path, mode):
     a = torch.load(full.ckpt_path(), weights_only=False)
     b = torch.load(j2.ckpt_path(), weights_only=False)
     assert _digest(a) == _digest(b)
+
+
+@needs2
+@pytest.mark.parametrize("reshard", ["0", "1"])
+def test_fsdp_sharded_gradients_track_one_gpu(reshard):
+    """FTL_FSDP_SHARD_GRADS=1: no model-sized gradient buffer (two layer-sized slots reused by the backward, compact
+    reduced shards), with resident and with re-gathered parameters: same trajectory, same checkpoint round trip."""
+    r, out = _torchrun(2, "tools/fsdp_check.py", env={"FTL_FSDP_SHARD_GRADS": "1", "FTL_FSDP_RESHARD": reshard})
+    assert r.returncode == 0 and out and out[0]["ok"], r.stdout[-2000:] + r.stderr[-2000:]
+    assert out[1]["resume_from_shards_equal"] and out[1]["resume_from_consolidated_equal"], out[1]
