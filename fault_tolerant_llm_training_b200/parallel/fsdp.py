@@ -1,8 +1,9 @@
 """Fully-sharded engine (ZeRO-3 style): BASELINE.json fused path 2 — the parameter all-gather is pulled into
 the QKV and gate/up GEMMs that consume the gathered weights.
 
-Persistent state per rank is only ITS row shard of every weight matrix (one compact peer-mapped buffer),
-the matching AdamW moments, and the local gradient buffer.  Gathered weights live in staging memory, bucket by
+Persistent state per rank is only ITS row shard of every weight matrix (one compact peer-mapped buffer), the
+matching AdamW moments and the reduced gradient shards; gradients are produced into two layer-sized slots that the
+backward reuses (plus one buffer each for the embedding and the head bucket), never into a model-sized buffer.  Gathered weights live in staging memory, bucket by
 bucket (bucket = embedding | layer i | final norm + head), in one of two modes:
 
   resident (default)   one staging buffer the size of the model (16 GB of the 180 GB HBM for the 8 B model): a bucket
@@ -139,13 +140,12 @@ class FsdpTrainer(PipelinedTrainer):
         flag_words = N.lib().ftl_comm_flag_words()
         # fully-sharded mode has no parameter broadcast; its gradient reduce-scatter can go through the switch too
         self.nvls = os.environ.get("FTL_COLLECTIVE", "p2p") == "nvls" and W > 1
-        # FTL_FSDP_SHARD_GRADS=1: no model-sized gradient buffer.  The embedding and the head bucket keep their own
+        # Sharded gradients (default; FTL_FSDP_SHARD_GRADS=0 keeps a model-sized buffer): the embedding and the head bucket keep their own
         # gradient buffers, the layers write into two layer-sized slots by bucket parity, and every reduce-scatter leaves
         # its result in a compact shard buffer; a slot is reused by the backward two layers later, once every rank has
         # finished reading it (a barrier after the reduce-scatter + an event the compute stream waits on).
-        self.shard_grads = os.environ.get("FTL_FSDP_SHARD_GRADS", "0") == "1" and W > 1
-        if self.shard_grads and self.nvls:
-            raise ValueError("FTL_FSDP_SHARD_GRADS=1 uses the peer-load reduce-scatter; unset FTL_COLLECTIVE=nvls")
+        # (the NVLS reduce-scatter needs one multicast mapping of the whole gradient buffer: it keeps the full buffer)
+        self.shard_grads = os.environ.get("FTL_FSDP_SHARD_GRADS", "1") != "0" and W > 1 and not self.nvls
         if self.shard_grads:
             layer_max = max(hi - lo for lo, hi in self.buckets[1:L + 1])
             gsizes = {"g0": (self.buckets[0][1] - self.buckets[0][0]) * 2,

@@ -158,9 +158,16 @@ def test_two_rank_usr1_chain_is_bitwise(tmp_path, mode):
 
 
 @needs2
+def test_fsdp_full_gradient_buffer_tracks_one_gpu():
+    """FTL_FSDP_SHARD_GRADS=0: the round-1 layout with a model-sized gradient buffer per rank."""
+    r, out = _torchrun(2, "tools/fsdp_check.py", env={"FTL_FSDP_SHARD_GRADS": "0"})
+    assert r.returncode == 0 and out and out[0]["ok"], r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@needs2
 @pytest.mark.parametrize("reshard", ["0", "1"])
 def test_fsdp_sharded_gradients_track_one_gpu(reshard):
-    """FTL_FSDP_SHARD_GRADS=1: no model-sized gradient buffer (two layer-sized slots reused by the backward, compact
+    """Sharded gradients (the default, set explicitly here): no model-sized gradient buffer (two layer-sized slots reused by the backward, compact
     reduced shards), with resident and with re-gathered parameters: same trajectory, same checkpoint round trip."""
     r, out = _torchrun(2, "tools/fsdp_check.py", env={"FTL_FSDP_SHARD_GRADS": "1", "FTL_FSDP_RESHARD": reshard})
     assert r.returncode == 0 and out and out[0]["ok"], r.stdout[-2000:] + r.stderr[-2000:]
