@@ -266,6 +266,8 @@ class NativeEngine:
         # slice per producing launch, handed out in launch order, summed in index order by the publish kernel.
         self.norm_arena: Optional[torch.Tensor] = None
         self._arena_off = 0
+        self.use_graphs = (os.environ.get("FTL_GRAPHS", "0") == "1" and self.USE_TC and self.own_attn)
+        self._graphs, self._steps_seen = {}, 0
         self.hook_params_bwd = None   # called before the backward of bucket b reads its parameters
         self.hook_tokens = None       # called at the start of the backward with the step's flat token ids
         self.fused_gather = None      # FSDP: object with qkv(i, x, out) / swiglu(i, x, act, gate, up) running the
@@ -363,6 +365,94 @@ class NativeEngine:
         d[:, (H + KV) * hd:].view(B, S, KV, hd).copy_(dv.transpose(1, 2))
         self.attn[i] = self.attn_in[i] = None
 
+    # ---- per-layer CUDA graphs (FTL_GRAPHS=1) ---------------------------------------------------------------------
+    # A block's forward is 7 launches and its backward 13, all over static buffers: after two eager steps (so that every
+    # one-time attribute call and scratch allocation has happened) each is captured once and replayed, which removes
+    # the 2-5 us launch gaps inside a block (~1.9 ms of a step's compute stream, profiles/step_gaps_r1.md).  Everything
+    # that takes a host-side decision stays outside the graphs: parameter / gradient hooks (event waits, reduce-scatter
+    # launches), the head, the embedding.
+    def _layer(self, kind: str, i: int, fn, *args) -> None:
+        # (the fully-sharded engine keeps host-side bookkeeping inside its gather-fused GEMM calls: no graphs there)
+        if not self.use_graphs or self.fused_gather is not None or self.hook_params_bwd is not None:
+            return fn(*args)
+        key = (kind, i)
+        g = self._graphs.get(key)
+        if g is not None:
+            g[0].replay()
+            self._arena_off = g[1]
+            N.KERNELS += g[2]                             # the kernels inside the graph ran: keep the launch count honest
+            N.LAUNCHES += 1
+            return
+        if self._steps_seen < 2:
+            return fn(*args)
+        graph, k0 = torch.cuda.CUDAGraph(), N.KERNELS
+        with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+            fn(*args)
+        # the partial-sum slices taken inside are baked into the graph; remember where the bump allocator ended
+        self._graphs[key] = (graph, self._arena_off, N.KERNELS - k0)
+        graph.replay()                                    # capture only records: run the block for this step
+
+    def _fwd_layer(self, i: int) -> None:
+        """The seven launches of block i's forward (no host-side decisions: capturable as one CUDA graph)."""
+        c, lw = self.cfg, self.lw[i]
+        H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        rot = (H + KV) * hd
+        # residual add of the previous block fused with this block's attention_norm (x_i = h_{i-1} + ff)
+        if i == 0:
+            N.rmsnorm_fwd(self.x[0], lw["wan"], c.norm_eps, self.xn[0], self.rstd1[0])
+        else:
+            N.rmsnorm_fwd(self.h[i - 1], lw["wan"], c.norm_eps, self.xn[i], self.rstd1[i], delta=self.ff, h_out=self.x[i])
+        if self.fused_gather is not None:   # FSDP: wq|wk|wv arrive over NVLink inside the GEMM (N12)
+            self.fused_gather.qkv(i, self.xn[i], self.qkv[i])
+        elif self.USE_TC:   # QKV projection with RoPE in the GEMM epilogue (K3 + K4)
+            N.gemm_qkv_rope(self.xn[i], lw["wqkv"], self.qkv[i], self.cos, self.sin, self.S, hd, rot)
+        else:
+            self.gemm_nt(self.xn[i], lw["wqkv"], self.qkv[i])
+            N.rope_inplace(self.qkv[i], self.cos, self.sin, self.S, rot, hd)
+        a = self._attention_fwd(i)
+        self.gemm_nt(a, lw["wo"], self.ao)
+        # h = x + attn_out ; hn = norm(h)
+        N.rmsnorm_fwd(self.x[i], lw["wfn"], c.norm_eps, self.hn[i], self.rstd2[i], delta=self.ao, h_out=self.h[i])
+        if self.fused_gather is not None:
+            self.fused_gather.swiglu(i, self.hn[i], self.act[i], self.gate[i], self.up[i])
+        elif self.USE_TC:   # gate|up dual GEMM with the SwiGLU epilogue (K9 + K10)
+            N.gemm_swiglu(self.hn[i], lw["ww1"], lw["ww3"], self.act[i], self.gate[i], self.up[i])
+        else:
+            self.gemm_nt(self.hn[i], lw["ww1"], self.gate[i])
+            self.gemm_nt(self.hn[i], lw["ww3"], self.up[i])
+            N.swiglu_fwd(self.gate[i], self.up[i], self.act[i])
+        self.gemm_nt(self.act[i], lw["ww2"], self.ff)
+
+    def _bwd_layer(self, i: int, dx: torch.Tensor, spare: torch.Tensor) -> None:
+        """The launches of block i's backward: d(x_{i+1}) in `dx` -> d(x_i) in `spare`, weight gradients in place."""
+        c, T, lw = self.cfg, self.T, self.lw[i]
+        H, KV, hd = c.n_heads, c.n_kv_heads, c.head_dim
+        rot = (H + KV) * hd
+        # x_{i+1} = h + w2(act)
+        self.gemm_tn(dx, self.act[i], lw["gw2"])
+        if self.fused_swiglu_bwd:   # d act -> (d gate, d up) in the dgrad epilogue
+            N.gemm_swiglu_bwd(dx, lw["ww2"], self.gate[i], self.up[i], self.dgate, self.dup)
+        else:
+            self.gemm_nn(dx, lw["ww2"], self.dact)
+            N.swiglu_bwd(self.dact, self.gate[i], self.up[i], self.dgate, self.dup)
+        self.gemm_tn(self.dgate, self.hn[i], lw["gw1"])
+        self.gemm_tn(self.dup, self.hn[i], lw["gw3"])
+        self.gemm_nn(self.dgate, lw["ww1"], self.dtmp, a2=self.dup, b2=lw["ww3"])   # one pass over K = 2F
+        # dh = dx + d ffn_norm
+        N.rmsnorm_bwd(self.dtmp, self.h[i], lw["wfn"], self.rstd2[i], self.dh, lw["gfn"], self.norm_scratch,
+                      dres=dx, sumsq=self._sq_norm())
+        # h = x + wo(attn)
+        a = self.attn_o[i] if self.own_attn else self.attn[i].transpose(1, 2).reshape(T, H * hd)
+        self.gemm_tn(self.dh, a, lw["go"])
+        self.gemm_nn(self.dh, lw["wo"], self.dattn)
+        self._attention_bwd(i, self.dattn)
+        if not self.own_attn:
+            N.rope_inplace(self.dqkv, self.cos, self.sin, self.S, rot, hd, inverse=True)
+        self.gemm_tn(self.dqkv, self.xn[i], lw["gqkv"])
+        self.gemm_nn(self.dqkv, lw["wqkv"], self.dtmp)
+        N.rmsnorm_bwd(self.dtmp, self.x[i], lw["wan"], self.rstd1[i], spare, lw["gan"], self.norm_scratch,
+                      dres=self.dh, sumsq=self._sq_norm())
+
     # ---- forward ---------------------------------------------------------------------------------
     @torch.no_grad()
     def forward(self, tokens: torch.Tensor, labels: torch.Tensor, inv_n: torch.Tensor, write_grad: bool = True):
@@ -378,31 +468,7 @@ class NativeEngine:
                 _Nvtx.pop()
             _Nvtx.push(f"fwd layer {i}")
             self._need(i + 1)
-            # residual add of the previous block fused with this block's attention_norm (x_i = h_{i-1} + ff)
-            if i == 0:
-                N.rmsnorm_fwd(self.x[0], lw["wan"], c.norm_eps, self.xn[0], self.rstd1[0])
-            else:
-                N.rmsnorm_fwd(self.h[i - 1], lw["wan"], c.norm_eps, self.xn[i], self.rstd1[i], delta=self.ff, h_out=self.x[i])
-            if self.fused_gather is not None:   # FSDP: wq|wk|wv arrive over NVLink inside the GEMM (N12)
-                self.fused_gather.qkv(i, self.xn[i], self.qkv[i])
-            elif self.USE_TC:   # QKV projection with RoPE in the GEMM epilogue (K3 + K4)
-                N.gemm_qkv_rope(self.xn[i], lw["wqkv"], self.qkv[i], self.cos, self.sin, self.S, hd, rot)
-            else:
-                self.gemm_nt(self.xn[i], lw["wqkv"], self.qkv[i])
-                N.rope_inplace(self.qkv[i], self.cos, self.sin, self.S, rot, hd)
-            a = self._attention_fwd(i)
-            self.gemm_nt(a, lw["wo"], self.ao)
-            # h = x + attn_out ; hn = norm(h)
-            N.rmsnorm_fwd(self.x[i], lw["wfn"], c.norm_eps, self.hn[i], self.rstd2[i], delta=self.ao, h_out=self.h[i])
-            if self.fused_gather is not None:
-                self.fused_gather.swiglu(i, self.hn[i], self.act[i], self.gate[i], self.up[i])
-            elif self.USE_TC:   # gate|up dual GEMM with the SwiGLU epilogue (K9 + K10)
-                N.gemm_swiglu(self.hn[i], lw["ww1"], lw["ww3"], self.act[i], self.gate[i], self.up[i])
-            else:
-                self.gemm_nt(self.hn[i], lw["ww1"], self.gate[i])
-                self.gemm_nt(self.hn[i], lw["ww3"], self.up[i])
-                N.swiglu_fwd(self.gate[i], self.up[i], self.act[i])
-            self.gemm_nt(self.act[i], lw["ww2"], self.ff)
+            self._layer("f", i, self._fwd_layer, i)
         L = c.n_layers
         _Nvtx.pop()
         _Nvtx.push("fwd head + loss")
@@ -450,30 +516,7 @@ class NativeEngine:
             _Nvtx.push(f"bwd layer {i}")
             if self.hook_params_bwd is not None:
                 self.hook_params_bwd(i + 1)
-            # x_{i+1} = h + w2(act)
-            self.gemm_tn(dx, self.act[i], lw["gw2"])
-            if self.fused_swiglu_bwd:   # d act -> (d gate, d up) in the dgrad epilogue
-                N.gemm_swiglu_bwd(dx, lw["ww2"], self.gate[i], self.up[i], self.dgate, self.dup)
-            else:
-                self.gemm_nn(dx, lw["ww2"], self.dact)
-                N.swiglu_bwd(self.dact, self.gate[i], self.up[i], self.dgate, self.dup)
-            self.gemm_tn(self.dgate, self.hn[i], lw["gw1"])
-            self.gemm_tn(self.dup, self.hn[i], lw["gw3"])
-            self.gemm_nn(self.dgate, lw["ww1"], self.dtmp, a2=self.dup, b2=lw["ww3"])   # one pass over K = 2F
-            # dh = dx + d ffn_norm
-            N.rmsnorm_bwd(self.dtmp, self.h[i], lw["wfn"], self.rstd2[i], self.dh, lw["gfn"], self.norm_scratch,
-                          dres=dx, sumsq=self._sq_norm())
-            # h = x + wo(attn)
-            a = self.attn_o[i] if self.own_attn else self.attn[i].transpose(1, 2).reshape(T, H * hd)
-            self.gemm_tn(self.dh, a, lw["go"])
-            self.gemm_nn(self.dh, lw["wo"], self.dattn)
-            self._attention_bwd(i, self.dattn)
-            if not self.own_attn:
-                N.rope_inplace(self.dqkv, self.cos, self.sin, self.S, rot, hd, inverse=True)
-            self.gemm_tn(self.dqkv, self.xn[i], lw["gqkv"])
-            self.gemm_nn(self.dqkv, lw["wqkv"], self.dtmp)
-            N.rmsnorm_bwd(self.dtmp, self.x[i], lw["wan"], self.rstd1[i], spare, lw["gan"], self.norm_scratch,
-                          dres=self.dh, sumsq=self._sq_norm())
+            self._layer("b", i, self._bwd_layer, i, dx, spare)
             dx, spare = spare, dx
             if self.hook_grads is not None:
                 self.hook_grads(i + 1)
@@ -498,6 +541,7 @@ class NativeEngine:
             self.hook_grads(0)
         _Nvtx.pop()
         _Nvtx.pop()
+        self._steps_seen += 1
 
 
 # --------------------------------------------------------------------------------------------------
