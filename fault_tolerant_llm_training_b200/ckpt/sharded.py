@@ -155,6 +155,12 @@ class FlatCheckpointer:
         self._pending = (d, checkpoint_file(checkpoint_path, jobid), jobid)
         return d
 
+    def drop_predecessor(self, logger=None) -> None:
+        """Public form for the training driver: called on rank 0 when a resumed job ends without writing a checkpoint of
+        its own, so that the shards it resumed from do not stay behind for ever."""
+        if self.t.env.is_main:
+            self._drop_predecessor(logger)
+
     def _drop_predecessor(self, logger=None) -> None:
         """This job's own checkpoint is durable: the shards of the checkpoint it resumed from are no longer needed
         by anyone, provided the job that wrote them has finished consolidating (its .ckpt exists)."""

@@ -133,7 +133,10 @@ class BatchStream:
     rank; its own state_dict is stored.
 
     A background thread tokenises ahead (the reference tokenises on the training
-    thread); batches are delivered in pinned memory when asked.
+    thread); batches are delivered in pinned memory when asked.  Pinned
+    batches are views into a ring of `prefetch + 8` page-locked buffers allocated
+    once: a consumer that wants to keep a batch beyond the next few must copy it
+    (the trainers copy every batch into their own staging memory inside `step()`).
     """
 
     def __init__(self, dataset, batch_size: int, collator: Optional[CollatorForCLM] = None,

@@ -186,6 +186,8 @@ def train(args) -> None:
         if args.save_final:
             _save_now(trainer, args, training_step, stream, env)
             logger.info(f"Final checkpoint saved at step {training_step}")
+        elif hasattr(trainer, "checkpointer"):
+            trainer.checkpointer.drop_predecessor(logger)   # nothing of ours replaces them: remove the shards we resumed from
     except Exception as e:  # noqa: BLE001 — every interruption goes through the same handler (train.py:121-129)
         error_type = error_type_of(e)
         if error_type == -1 and not (len(e.args) >= 2 and e.args[1] == -1):
