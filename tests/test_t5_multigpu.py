@@ -23,7 +23,11 @@ pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NGPU = torch.cuda.device_count() if torch.cuda.is_available() else 0
-WORLDS = [w for w in (2, 4, 8) if w <= NGPU]
+# world sizes of the trajectory tests: 2 and the largest power of two the box has (FTL_TEST_WORLDS=2,4,8 runs them all;
+# every size costs a torchrun start-up per test, and W = 4 adds no code path that W = 2 and W = 8 do not take)
+_all = [w for w in (2, 4, 8) if w <= NGPU]
+WORLDS = ([int(x) for x in os.environ["FTL_TEST_WORLDS"].split(",") if int(x) <= NGPU] if os.environ.get("FTL_TEST_WORLDS")
+          else sorted({w for w in _all if w == 2 or w == max(_all)}))
 needs2 = pytest.mark.skipif(NGPU < 2, reason="needs at least 2 GPUs")
 
 
