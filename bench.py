@@ -157,7 +157,7 @@ def _measure_ours(a, env, cfg, tok, data, parallel: str, ckpt: bool) -> dict:
     if ckpt:
         # 6 bytes per parameter (bf16 p, m, v) go to /tmp: skip with a reason rather than die when the box is short of disk
         import shutil
-        need = 6 * cfg.num_params() * 1.05
+        need = 6 * cfg.num_params() + (256 << 20)
         free = min(env.gather_objects(shutil.disk_usage("/tmp").free))
         if free < need:
             res["ckpt"] = {"unavailable": f"/tmp has {free / 1e9:.0f} GB free, the checkpoint needs {need / 1e9:.0f} GB"}
